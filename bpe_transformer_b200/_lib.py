@@ -1,0 +1,299 @@
+"""ctypes binding of libbpe_b200.so (include/bpe_b200.h) and the per-GPU engine the Python API sits on.
+
+There is NO CPU fallback: if the library is missing or no CUDA device is present, everything here raises.
+PyTorch is used for device buffers, pinned host buffers and the current stream only.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import pathlib
+import threading
+
+import numpy as np
+
+CSRC = pathlib.Path(__file__).resolve().parent / "csrc"
+LIB_PATH = CSRC / "libbpe_b200.so"
+
+TEXT_PAD = 64
+CUT_AFTER_NEWLINE = 1
+
+OK, ERR_CUDA, ERR_INVALID_UTF8, ERR_CAPACITY, ERR_ARGUMENT, ERR_HASH_COLLISION, ERR_MISSING_ID, ERR_NO_PAIRS, ERR_STATE = range(9)
+
+SYMBOLS = [
+    "bpe_ctx_create", "bpe_ctx_destroy", "bpe_last_error", "bpe_ctx_configure", "bpe_set_special_tokens", "bpe_scan",
+    "bpe_count", "bpe_unique_stats", "bpe_unique_export", "bpe_unique_import", "bpe_unique_reset", "bpe_train",
+    "bpe_train_timing", "bpe_load_model", "bpe_encode", "bpe_decode", "bpe_kernel_times", "bpe_set_profiling",
+]
+
+
+class BpeError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libbpe_b200 error {code}: {message}")
+        self.code = code
+
+
+class InvalidUtf8(BpeError):
+    pass
+
+
+class KernelTime(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("ms", C.c_double), ("launches", C.c_uint64)]
+
+
+_lib = None
+_lib_lock = threading.Lock()
+
+
+def load_library():
+    """dlopen the in-tree library; fails loudly when it has not been built (python __graft_entry__.py build)."""
+    global _lib
+    with _lib_lock:
+        if _lib is not None:
+            return _lib
+        if not LIB_PATH.exists():
+            raise ImportError(f"{LIB_PATH} is missing: build it with `make -C {CSRC}` (or __graft_entry__.build()); "
+                              "there is no CPU fallback")
+        lib = C.CDLL(str(LIB_PATH))
+        vp, u8p, u32p, u64p = C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p
+        lib.bpe_ctx_create.argtypes = [C.c_int, C.POINTER(vp)]
+        lib.bpe_ctx_destroy.argtypes = [vp]
+        lib.bpe_ctx_destroy.restype = None
+        lib.bpe_last_error.argtypes = [vp]
+        lib.bpe_last_error.restype = C.c_char_p
+        lib.bpe_ctx_configure.argtypes = [vp, C.c_int, C.c_uint64]
+        lib.bpe_set_special_tokens.argtypes = [vp, u8p, u32p, C.c_int]
+        lib.bpe_scan.argtypes = [vp, u8p, C.c_uint64, u64p, C.c_uint64, C.c_uint32, u32p, vp]
+        lib.bpe_count.argtypes = [vp, u8p, C.c_uint64, u32p, vp]
+        lib.bpe_unique_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        lib.bpe_unique_export.argtypes = [vp, u8p, u64p, u32p, u64p, vp]
+        lib.bpe_unique_import.argtypes = [vp, u8p, u64p, u32p, u64p, C.c_uint64, vp]
+        lib.bpe_unique_reset.argtypes = [vp]
+        lib.bpe_train.argtypes = [vp, C.c_uint32, C.c_uint32, u8p, u32p, u32p, u32p, C.POINTER(C.c_uint32), vp]
+        lib.bpe_train_timing.argtypes = [vp, C.POINTER(C.c_double)]
+        lib.bpe_load_model.argtypes = [vp, u32p, u32p, u32p, C.c_uint32, u32p, u32p]
+        lib.bpe_encode.argtypes = [vp, u8p, C.c_uint64, u64p, C.c_uint64, C.c_uint32, u32p, vp, C.c_int, C.c_uint64,
+                                   C.POINTER(C.c_uint64), vp]
+        lib.bpe_decode.argtypes = [vp, vp, C.c_int, C.c_uint64, u8p, u64p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_uint64), vp]
+        lib.bpe_kernel_times.argtypes = [vp, C.POINTER(KernelTime), C.c_int]
+        lib.bpe_set_profiling.argtypes = [vp, C.c_int]
+        for name in SYMBOLS:
+            fn = getattr(lib, name)
+            if name not in ("bpe_ctx_destroy", "bpe_last_error"):
+                fn.restype = C.c_int
+        _lib = lib
+        return lib
+
+
+def _np_ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def sort_specials(special_tokens) -> list[bytes]:
+    """Match priority of the reference's split_on_special_tokens (pretokenization.py:228): longest first,
+    ties in the given order (sorted() is stable)."""
+    toks = [s.encode("utf-8") if isinstance(s, str) else bytes(s) for s in (special_tokens or [])]
+    return sorted(toks, key=len, reverse=True)
+
+
+class Engine:
+    """One libbpe_b200 context on one GPU plus the torch buffers around it."""
+
+    def __init__(self, device: int | None = None, table_log2: int | None = None, pool_bytes: int | None = None):
+        import torch
+
+        if not torch.cuda.is_available():
+            raise RuntimeError("bpe_transformer_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.torch = torch
+        self.lib = load_library()
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        torch.cuda.set_device(self.device)
+        torch.cuda.init()
+        torch.zeros(1, device=f"cuda:{self.device}")  # make sure the primary context exists before the library uses it
+        ctx = C.c_void_p()
+        rc = self.lib.bpe_ctx_create(self.device, C.byref(ctx))
+        if rc:
+            raise BpeError(rc, (self.lib.bpe_last_error(None) or b"").decode())
+        self.ctx = ctx
+        self._specials: list[bytes] | None = None
+        self._model_token = None
+        if table_log2 is not None or pool_bytes is not None:
+            self.configure(table_log2 or 22, pool_bytes or (256 << 20))
+
+    # -- plumbing ----------------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.bpe_ctx_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int):
+        if rc == OK:
+            return
+        msg = (self.lib.bpe_last_error(self.ctx) or b"").decode()
+        if rc == ERR_INVALID_UTF8:
+            raise InvalidUtf8(rc, msg)
+        raise BpeError(rc, msg)
+
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    def configure(self, table_log2: int, pool_bytes: int):
+        self._check(self.lib.bpe_ctx_configure(self.ctx, int(table_log2), int(pool_bytes)))
+        self._model_token = None
+
+    def set_profiling(self, on: bool):
+        self._check(self.lib.bpe_set_profiling(self.ctx, 1 if on else 0))
+
+    def kernel_times(self) -> dict[str, tuple[float, int]]:
+        buf = (KernelTime * 32)()
+        n = self.lib.bpe_kernel_times(self.ctx, buf, 32)
+        return {buf[i].name.decode(): (buf[i].ms, int(buf[i].launches)) for i in range(n)}
+
+    # -- buffers -----------------------------------------------------------------------------------------
+    def to_device(self, data) -> tuple["object", int]:
+        """bytes / bytearray / numpy uint8 / pinned torch uint8 -> padded device tensor and its length."""
+        torch = self.torch
+        if isinstance(data, torch.Tensor):
+            host = data
+        else:
+            host = torch.frombuffer(memoryview(data), dtype=torch.uint8) if len(data) else torch.empty(0, dtype=torch.uint8)
+        n = int(host.numel())
+        dev = torch.empty(n + TEXT_PAD, dtype=torch.uint8, device=f"cuda:{self.device}")
+        if n:
+            dev[:n].copy_(host, non_blocking=True)
+        return dev, n
+
+    def new_mask(self, n: int):
+        return self.torch.empty(n // 32 + 2, dtype=self.torch.int32, device=f"cuda:{self.device}")
+
+    # -- the C-ABI calls -----------------------------------------------------------------------------------
+    def set_special_tokens(self, specials: list[bytes]):
+        if self._specials == specials:
+            return
+        blob = np.frombuffer(b"".join(specials) + b"\0", dtype=np.uint8).copy()
+        off = np.zeros(len(specials) + 1, dtype=np.uint32)
+        if specials:
+            off[1:] = np.cumsum([len(s) for s in specials])
+        self._check(self.lib.bpe_set_special_tokens(self.ctx, _np_ptr(blob), _np_ptr(off), len(specials)))
+        self._specials = list(specials)
+        self._model_token = None  # special ids are part of the loaded model
+
+    def scan(self, d_text, n: int, cuts=None, flags: int = 0):
+        torch = self.torch
+        mask = self.new_mask(n)
+        d_cuts, n_cuts = None, 0
+        if cuts is not None and len(cuts):
+            d_cuts = torch.as_tensor(np.asarray(cuts, dtype=np.int64), device=f"cuda:{self.device}")
+            n_cuts = int(d_cuts.numel())
+        self._check(self.lib.bpe_scan(self.ctx, d_text.data_ptr(), n, d_cuts.data_ptr() if d_cuts is not None else None, n_cuts,
+                                      flags, mask.data_ptr(), self._stream()))
+        return mask
+
+    def count(self, d_text, n: int, mask):
+        self._check(self.lib.bpe_count(self.ctx, d_text.data_ptr(), n, mask.data_ptr(), self._stream()))
+
+    def unique_stats(self) -> tuple[int, int, int]:
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._check(self.lib.bpe_unique_stats(self.ctx, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def unique_reset(self):
+        self._check(self.lib.bpe_unique_reset(self.ctx))
+
+    def unique_export(self):
+        """(blob uint8, off int64, len int32, cnt int64) device tensors."""
+        torch = self.torch
+        n_unique, n_bytes, _ = self.unique_stats()
+        dev = f"cuda:{self.device}"
+        blob = torch.zeros(n_bytes + TEXT_PAD, dtype=torch.uint8, device=dev)
+        off = torch.zeros(max(n_unique, 1), dtype=torch.int64, device=dev)
+        ln = torch.zeros(max(n_unique, 1), dtype=torch.int32, device=dev)
+        cnt = torch.zeros(max(n_unique, 1), dtype=torch.int64, device=dev)
+        if n_unique:
+            self._check(self.lib.bpe_unique_export(self.ctx, blob.data_ptr(), off.data_ptr(), ln.data_ptr(), cnt.data_ptr(), self._stream()))
+        return blob, off[:n_unique], ln[:n_unique], cnt[:n_unique]
+
+    def unique_import(self, blob, off, ln, cnt):
+        n = int(off.numel())
+        if n:
+            self._check(self.lib.bpe_unique_import(self.ctx, blob.data_ptr(), off.data_ptr(), ln.data_ptr(), cnt.data_ptr(), n, self._stream()))
+
+    def train(self, vocab_size: int, init_tokens: list[bytes]) -> tuple[np.ndarray, np.ndarray]:
+        first_new = len(init_tokens)
+        blob = np.frombuffer(b"".join(init_tokens) + b"\0", dtype=np.uint8).copy()
+        off = np.zeros(first_new + 1, dtype=np.uint32)
+        off[1:] = np.cumsum([len(t) for t in init_tokens])
+        cap = max(1, vocab_size - first_new)
+        ma = np.zeros(cap, dtype=np.uint32)
+        mb = np.zeros(cap, dtype=np.uint32)
+        nm = C.c_uint32(0)
+        self._check(self.lib.bpe_train(self.ctx, vocab_size, first_new, _np_ptr(blob), _np_ptr(off), _np_ptr(ma), _np_ptr(mb),
+                                       C.byref(nm), self._stream()))
+        return ma[:nm.value], mb[:nm.value]
+
+    def train_timing(self) -> tuple[float, float, int]:
+        out = (C.c_double * 3)()
+        self._check(self.lib.bpe_train_timing(self.ctx, out))
+        return out[0], out[1], int(out[2])
+
+    def load_model(self, token, m_a, m_b, m_id, byte_to_id, special_id):
+        """`token` identifies the model; reloading the same one is skipped (it would drop the encoding cache)."""
+        if self._model_token is not None and self._model_token == token:
+            return
+        m_a = np.ascontiguousarray(m_a, dtype=np.uint32)
+        m_b = np.ascontiguousarray(m_b, dtype=np.uint32)
+        m_id = np.ascontiguousarray(m_id, dtype=np.uint32)
+        b2i = np.ascontiguousarray(byte_to_id, dtype=np.uint32)
+        sid = np.ascontiguousarray(list(special_id) + [0], dtype=np.uint32)
+        self._check(self.lib.bpe_load_model(self.ctx, _np_ptr(m_a), _np_ptr(m_b), _np_ptr(m_id), len(m_a), _np_ptr(b2i), _np_ptr(sid)))
+        self._model_token = token
+
+    def encode(self, d_text, n: int, cuts=None, flags: int = 0, wide: bool = False, mask=None):
+        """Returns a device tensor of ids (int16 bit pattern = uint16, or int32)."""
+        torch = self.torch
+        dev = f"cuda:{self.device}"
+        d_cuts, n_cuts = None, 0
+        if cuts is not None and len(cuts):
+            d_cuts = torch.as_tensor(np.asarray(cuts, dtype=np.int64), device=dev)
+            n_cuts = int(d_cuts.numel())
+        out = torch.empty(n + 1, dtype=torch.int32 if wide else torch.int16, device=dev)
+        n_out = C.c_uint64(0)
+        self._check(self.lib.bpe_encode(self.ctx, d_text.data_ptr(), n, d_cuts.data_ptr() if d_cuts is not None else None, n_cuts,
+                                        flags, mask.data_ptr() if mask is not None else None, out.data_ptr(), 4 if wide else 2,
+                                        n + 1, C.byref(n_out), self._stream()))
+        return out[:n_out.value]
+
+    def decode(self, d_ids, vocab_blob: np.ndarray, vocab_off: np.ndarray, max_token_len: int):
+        torch = self.torch
+        n_ids = int(d_ids.numel())
+        elem = d_ids.element_size()
+        cap = n_ids * max(3, max_token_len) + 16
+        out = torch.empty(cap, dtype=torch.uint8, device=f"cuda:{self.device}")
+        n_bytes = C.c_uint64(0)
+        self._check(self.lib.bpe_decode(self.ctx, d_ids.data_ptr(), elem, n_ids, _np_ptr(vocab_blob), _np_ptr(vocab_off),
+                                        len(vocab_off) - 1, out.data_ptr(), cap, C.byref(n_bytes), self._stream()))
+        return out[:n_bytes.value]
+
+
+_engines: dict[int, Engine] = {}
+
+
+def get_engine(device: int | None = None) -> Engine:
+    """The process-wide engine of a GPU (created on first use)."""
+    import torch
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("bpe_transformer_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    dev = torch.cuda.current_device() if device is None else int(device)
+    eng = _engines.get(dev)
+    if eng is None:
+        eng = Engine(dev, table_log2=int(os.environ.get("BPE_B200_TABLE_LOG2", "22")),
+                     pool_bytes=int(os.environ.get("BPE_B200_POOL_BYTES", str(256 << 20))))
+        _engines[dev] = eng
+    return eng

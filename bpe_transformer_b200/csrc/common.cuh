@@ -1,0 +1,284 @@
+// common.cuh — shared device helpers and the context layout of libbpe_b200.so (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/bpe_b200.h"
+
+#define BPE_N_SM 148  // B200: 2 dies x 74 SMs; persistent grids are sized in multiples of this
+
+// ---- status word written by kernels (one per context, in device memory) --------------------------------
+enum : uint32_t {
+    ST_INVALID_UTF8 = 1u << 0,
+    ST_TABLE_FULL = 1u << 1,
+    ST_POOL_FULL = 1u << 2,
+    ST_COLLISION = 1u << 3,
+    ST_MISSING_ID = 1u << 4,
+    ST_PAIR_TABLE_FULL = 1u << 5,
+    ST_LIST_FULL = 1u << 6,
+};
+
+// ---- code-point classes (include/bpe_unicode_tables.h) --------------------------------------------------
+enum : uint32_t { CLS_O = 0, CLS_L = 1, CLS_N = 2, CLS_S = 3 };
+
+struct ClassTables {
+    const uint8_t* stage1;   // BPE_UC_N_STAGE1 block ids
+    const uint32_t* stage2;  // 16 words (256 code points x 2 bits) per block
+    uint32_t n_stage1;
+};
+
+__device__ __forceinline__ uint32_t cp_class(const ClassTables& t, uint32_t cp) {
+    uint32_t b = cp >> 8;
+    if (b >= t.n_stage1) return CLS_O;
+    uint32_t w = __ldg(t.stage2 + (uint32_t)__ldg(t.stage1 + b) * 16u + ((cp & 255u) >> 4));
+    return (w >> (2u * (cp & 15u))) & 3u;
+}
+
+// ---- special tokens (few, short): passed by value to kernels ---------------------------------------------
+#define BPE_MAX_SPECIALS 16
+#define BPE_MAX_SPECIAL_BYTES 256
+struct Specials {
+    int n;
+    int max_len;
+    uint32_t off[BPE_MAX_SPECIALS + 1];
+    uint32_t first_byte_mask[8];  // 256-bit set of first bytes
+    uint8_t blob[BPE_MAX_SPECIAL_BYTES];
+};
+
+// Index of the first special token (priority order) that matches text at p and fits below `limit`; -1 if none.
+__device__ __forceinline__ int special_at(const Specials& sp, const uint8_t* __restrict__ text, uint64_t p, uint64_t limit) {
+    uint8_t b0 = text[p];
+    if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return -1;
+    for (int s = 0; s < sp.n; s++) {
+        uint32_t len = sp.off[s + 1] - sp.off[s];
+        if (p + len > limit) continue;
+        bool ok = true;
+        for (uint32_t k = 0; k < len && ok; k++) ok = text[p + k] == sp.blob[sp.off[s] + k];
+        if (ok) return s;
+    }
+    return -1;
+}
+
+// ---- 64-bit key + 32-bit check of a byte string ---------------------------------------------------------
+// Internal to the library (the oracle compares byte strings, never hashes).  Eight bytes per round.
+__device__ __forceinline__ uint64_t mix64(uint64_t h, uint64_t w) {
+    h = (h ^ w) * 0x9FB21C651E98DF25ull;
+    return h ^ (h >> 35);
+}
+__device__ __forceinline__ uint32_t mix32(uint32_t h, uint64_t w) {
+    h = (h ^ (uint32_t)w) * 0x85EBCA6Bu;
+    h = (h ^ (uint32_t)(w >> 32) ^ (h >> 15)) * 0xC2B2AE35u;
+    return h ^ (h >> 13);
+}
+
+// Unaligned little-endian 64-bit read through two aligned reads (the buffer is padded: BPE_TEXT_PAD).
+__device__ __forceinline__ uint64_t load_u64_unaligned(const uint8_t* __restrict__ base, uint64_t p) {
+    const uint64_t* q = reinterpret_cast<const uint64_t*>(base) + (p >> 3);
+    uint32_t sh = (uint32_t)(p & 7) * 8u;
+    uint64_t lo = __ldg(q);
+    if (sh == 0) return lo;
+    uint64_t hi = __ldg(q + 1);
+    return (lo >> sh) | (hi << (64u - sh));
+}
+
+struct TokenKey {
+    uint64_t key;  // never 0
+    uint32_t chk;  // never 0
+};
+
+__device__ __forceinline__ TokenKey hash_bytes(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
+    uint64_t h = 0x243F6A8885A308D3ull ^ (len * 0x9E3779B97F4A7C15ull);
+    uint32_t c = 0x13198A2Eu ^ (uint32_t)len;
+    uint64_t o = 0;
+    for (; o + 8 <= len; o += 8) {
+        uint64_t w = load_u64_unaligned(base, p + o);
+        h = mix64(h, w);
+        c = mix32(c, w);
+    }
+    if (o < len) {
+        uint64_t w = load_u64_unaligned(base, p + o) & ((1ull << ((len - o) * 8)) - 1ull);
+        h = mix64(h, w);
+        c = mix32(c, w);
+    }
+    h ^= h >> 29;
+    TokenKey k;
+    k.key = h ? h : 1ull;
+    k.chk = c ? c : 1u;
+    return k;
+}
+
+// ---- the table of distinct pretokens (context-owned, global memory) ---------------------------------------
+struct UniqueTable {
+    uint64_t* key;       // [cap] 0 = empty
+    uint64_t* cnt;       // [cap] occurrences
+    uint64_t* pool_off;  // [cap] offset of the bytes in `pool`
+    uint32_t* len;       // [cap]
+    uint32_t* chk;       // [cap] 0 until the inserting thread has published
+    uint32_t* enc_off;   // [cap] offset of the cached encoding in the id pool (encode path)
+    uint32_t* enc_len;   // [cap] 0xFFFFFFFF = not encoded yet
+    uint8_t* pool;
+    uint64_t cap_mask;
+    uint64_t pool_cap;
+    uint64_t* counters;  // [0] pool cursor, [1] distinct, [2] total occurrences, [3] id-pool cursor
+};
+
+__device__ __forceinline__ void set_status(uint32_t* status, uint32_t bit) { atomicOr(status, bit); }
+
+// Adds `c` occurrences of text[p, p+len) to the table (copies the bytes into the pool on first sight).
+// Returns the slot, or ~0 when the table is full.
+__device__ __forceinline__ uint64_t unique_insert(const UniqueTable& t, uint32_t* status, const uint8_t* __restrict__ text,
+                                                  uint64_t p, uint32_t len, TokenKey k, uint64_t c) {
+    uint64_t slot = (k.key * 0xD6E8FEB86659FD93ull >> 17) & t.cap_mask;
+    for (uint64_t probe = 0; probe <= t.cap_mask; probe++) {
+        uint64_t cur = *reinterpret_cast<volatile uint64_t*>(t.key + slot);
+        if (cur == 0) {
+            cur = atomicCAS(reinterpret_cast<unsigned long long*>(t.key + slot), 0ull, (unsigned long long)k.key);
+            if (cur == 0) {  // ours: copy the bytes, publish
+                uint64_t off = atomicAdd(reinterpret_cast<unsigned long long*>(t.counters + 0), (unsigned long long)len);
+                if (off + len > t.pool_cap) {
+                    set_status(status, ST_POOL_FULL);
+                } else {
+                    for (uint32_t i = 0; i < len; i++) t.pool[off + i] = text[p + i];
+                }
+                t.pool_off[slot] = off;
+                t.len[slot] = len;
+                t.enc_len[slot] = 0xFFFFFFFFu;
+                __threadfence();
+                *reinterpret_cast<volatile uint32_t*>(t.chk + slot) = k.chk;
+                atomicAdd(reinterpret_cast<unsigned long long*>(t.counters + 1), 1ull);
+                if (c) atomicAdd(reinterpret_cast<unsigned long long*>(t.cnt + slot), (unsigned long long)c);
+                return slot;
+            }
+        }
+        if (cur == k.key) {
+            uint32_t seen = *reinterpret_cast<volatile uint32_t*>(t.chk + slot);
+            if (seen != 0 && seen != k.chk) set_status(status, ST_COLLISION);
+            if (c) atomicAdd(reinterpret_cast<unsigned long long*>(t.cnt + slot), (unsigned long long)c);
+            return slot;
+        }
+        slot = (slot + 1) & t.cap_mask;
+    }
+    set_status(status, ST_TABLE_FULL);
+    return ~0ull;
+}
+
+// Slot of an already-counted pretoken, ~0 if absent.
+__device__ __forceinline__ uint64_t unique_find(const UniqueTable& t, TokenKey k) {
+    uint64_t slot = (k.key * 0xD6E8FEB86659FD93ull >> 17) & t.cap_mask;
+    for (uint64_t probe = 0; probe <= t.cap_mask; probe++) {
+        uint64_t cur = __ldg(t.key + slot);
+        if (cur == k.key) return slot;
+        if (cur == 0) return ~0ull;
+        slot = (slot + 1) & t.cap_mask;
+    }
+    return ~0ull;
+}
+
+// ---- bit helpers -----------------------------------------------------------------------------------------
+// End (exclusive) of the token that starts at bit `b` of start word `w` (word index wi), scanning forward.
+__device__ __forceinline__ uint64_t token_end(const uint32_t* __restrict__ start, uint64_t n_words, uint64_t wi, uint32_t w,
+                                              uint32_t b, uint64_t n) {
+    uint32_t rest = (b == 31) ? 0u : (w >> (b + 1));
+    if (rest) return wi * 32 + b + 1 + (__ffs(rest) - 1);
+    for (uint64_t j = wi + 1; j < n_words; j++) {
+        uint32_t x = __ldg(start + j);
+        if (x) {
+            uint64_t e = j * 32 + (__ffs(x) - 1);
+            return e < n ? e : n;
+        }
+    }
+    return n;
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------
+struct KernelTimer;
+
+struct bpe_ctx {
+    int device = 0;
+    std::string err;
+    uint32_t* d_status = nullptr;  // status word
+    ClassTables cls{};
+    uint8_t* d_stage1 = nullptr;
+    uint32_t* d_stage2 = nullptr;
+    Specials sp{};
+    // distinct pretokens
+    int table_log2 = 22;
+    uint64_t pool_bytes = 256ull << 20;
+    UniqueTable ut{};
+    bool ut_alloc = false;
+    // encode model
+    bool model_loaded = false;
+    uint64_t* d_mkey = nullptr;   // merge table: (a << 32 | b) + 1
+    uint32_t* d_mrank = nullptr;
+    uint32_t* d_mid = nullptr;
+    uint64_t m_mask = 0;
+    uint32_t* d_byte_to_id = nullptr;  // 256
+    uint32_t* d_special_id = nullptr;  // BPE_MAX_SPECIALS
+    uint32_t* d_idpool = nullptr;      // cached encodings of distinct pretokens
+    uint64_t idpool_cap = 0;
+    uint64_t enc_done = 0;             // number of distinct pretokens already encoded
+    // scratch reused across calls
+    void* scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    // timing
+    bool profiling = false;
+    std::vector<bpe_kernel_time> times;
+    double train_ms[3] = {0, 0, 0};
+};
+
+int ctx_fail(bpe_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess);
+void* ctx_scratch(bpe_ctx* ctx, int which, size_t bytes);  // grows-only device scratch, nullptr on failure
+int ctx_status_to_code(bpe_ctx* ctx, uint32_t st);
+uint32_t ctx_read_status(bpe_ctx* ctx, cudaStream_t s, bool clear = true);
+
+#define CUDA_TRY(ctx, expr)                                                      \
+    do {                                                                         \
+        cudaError_t e__ = (expr);                                                \
+        if (e__ != cudaSuccess) return ctx_fail((ctx), BPE_ERR_CUDA, #expr, e__); \
+    } while (0)
+
+// RAII CUDA-event timer that appends to ctx->times when profiling is on.
+struct KernelTimer {
+    bpe_ctx* ctx;
+    const char* name;
+    cudaStream_t s;
+    cudaEvent_t a = nullptr, b = nullptr;
+    KernelTimer(bpe_ctx* c, const char* nm, cudaStream_t st) : ctx(c), name(nm), s(st) {
+        if (ctx->profiling) {
+            cudaEventCreate(&a);
+            cudaEventCreate(&b);
+            cudaEventRecord(a, s);
+        }
+    }
+    ~KernelTimer() {
+        if (a) {
+            cudaEventRecord(b, s);
+            cudaEventSynchronize(b);
+            float ms = 0;
+            cudaEventElapsedTime(&ms, a, b);
+            bool found = false;
+            for (auto& t : ctx->times)
+                if (t.name == name) { t.ms += ms; t.launches++; found = true; }
+            if (!found) ctx->times.push_back({name, (double)ms, 1});
+            cudaEventDestroy(a);
+            cudaEventDestroy(b);
+        }
+    }
+};
+
+// kernels launched from api.cu, defined in the other translation units
+int launch_scan(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_cutmask, uint32_t flags, uint32_t* d_start, cudaStream_t s);
+int launch_cuts_to_mask(bpe_ctx* ctx, const uint64_t* d_cuts, uint64_t n_cuts, uint64_t n, uint32_t* d_cutmask, cudaStream_t s);
+int launch_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, cudaStream_t s);
+int launch_import(bpe_ctx* ctx, const uint8_t* d_blob, const uint64_t* d_off, const uint32_t* d_len, const uint64_t* d_cnt,
+                  uint64_t n_unique, cudaStream_t s);
+int launch_export(bpe_ctx* ctx, uint8_t* d_blob, uint64_t* d_off, uint32_t* d_len, uint64_t* d_cnt, cudaStream_t s);
+int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const uint8_t* h_init_blob, const uint32_t* h_init_off,
+              uint32_t* h_merge_a, uint32_t* h_merge_b, uint32_t* n_merges, cudaStream_t s);
+int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, void* d_out, int out_elem_bytes,
+               uint64_t cap, uint64_t* n_out, cudaStream_t s);
+int run_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_ids, const uint8_t* h_vocab_blob,
+               const uint64_t* h_vocab_off, uint32_t n_vocab, uint8_t* d_bytes, uint64_t cap, uint64_t* n_bytes, cudaStream_t s);

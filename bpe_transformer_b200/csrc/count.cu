@@ -1,0 +1,175 @@
+// count.cu — the Counter of distinct pretokens (pretokenize_chunk + the fold over workers in the reference:
+// bpe_transformer/tokenization/preprocessing/pretokenization.py:73-111, 171-208).
+//
+// Every thread owns one 32-bit word of the start mask (32 bytes of text).  For each set bit it finds the
+// token's end (next set bit), forms a 64-bit key + 32-bit check over the bytes (8 bytes per round, unaligned
+// 64-bit reads), and counts the key:
+//   1. in a per-CTA shared-memory table (4096 keys; Zipf text: the CTA's hot words live there), one
+//      shared-memory atomic per token;
+//   2. keys that do not fit go straight to the context's global table (L2-resident for ~10^5 keys);
+//   3. at the end of the CTA's range the shared table is folded into the global one, which also copies the
+//      bytes of a first-seen pretoken into the context's byte pool, so the text buffer is not needed later.
+// A CTA owns a CONTIGUOUS range of the text so that a representative position fits 32 bits.
+// HBM traffic: N bytes of text + N/8 of mask read; the tables stay in shared memory / L2.
+#include "common.cuh"
+
+#define COUNT_THREADS 512
+#define COUNT_SLOTS 4096  // per-CTA shared table: 8 B key + 4 B count + 4 B position + 4 B length = 20 B/slot = 80 KB
+#define COUNT_PROBES 8
+
+namespace {
+
+struct CountParams {
+    const uint8_t* text;
+    uint64_t n;
+    const uint32_t* start;
+    uint64_t n_words;          // words of the start mask that cover [0, n)
+    uint64_t words_per_block;  // contiguous range per CTA
+    uint32_t* status;
+    UniqueTable ut;
+};
+
+struct SharedTable {
+    unsigned long long key[COUNT_SLOTS];
+    uint32_t cnt[COUNT_SLOTS];
+    uint32_t pos[COUNT_SLOTS];  // byte position relative to the CTA's first byte
+    uint32_t len[COUNT_SLOTS];
+};
+
+__device__ __forceinline__ bool token_is_special(const Specials& sp, const uint8_t* __restrict__ text, uint64_t p, uint64_t len) {
+    uint8_t b0 = text[p];
+    if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return false;
+    for (int s = 0; s < sp.n; s++) {
+        if (sp.off[s + 1] - sp.off[s] != len) continue;
+        bool ok = true;
+        for (uint32_t k = 0; k < len && ok; k++) ok = text[p + k] == sp.blob[sp.off[s] + k];
+        if (ok) return true;
+    }
+    return false;
+}
+
+__global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams P, const __grid_constant__ Specials sp) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    SharedTable& st = *reinterpret_cast<SharedTable*>(smem_raw);
+    for (uint32_t k = threadIdx.x; k < COUNT_SLOTS; k += COUNT_THREADS) { st.key[k] = 0; st.cnt[k] = 0; }
+    __syncthreads();
+
+    const uint64_t w_lo = (uint64_t)blockIdx.x * P.words_per_block;
+    const uint64_t w_hi = (w_lo + P.words_per_block < P.n_words) ? w_lo + P.words_per_block : P.n_words;
+    const uint64_t base = w_lo * 32;  // first byte of this CTA's range
+    uint64_t local_tokens = 0;
+
+    for (uint64_t wi = w_lo + threadIdx.x; wi < w_hi; wi += COUNT_THREADS) {
+        uint32_t w = __ldg(P.start + wi);
+        for (uint32_t m = w; m; m &= m - 1) {
+            uint32_t b = __ffs(m) - 1;
+            uint64_t p = wi * 32 + b;
+            uint64_t e = token_end(P.start, P.n_words, wi, w, b, P.n);
+            uint64_t len = e - p;
+            if (sp.n && token_is_special(sp, P.text, p, len)) continue;
+            TokenKey k = hash_bytes(P.text, p, len);
+            local_tokens++;
+            bool done = false;
+            if (len < 0xFFFFFFFFull && p - base < 0xFFFFFFFFull) {
+                uint32_t slot = (uint32_t)(k.key >> 40) & (COUNT_SLOTS - 1);
+#pragma unroll 1
+                for (int probe = 0; probe < COUNT_PROBES && !done; probe++) {
+                    unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&st.key[slot]);
+                    if (cur == 0) {
+                        cur = atomicCAS(&st.key[slot], 0ull, (unsigned long long)k.key);
+                        if (cur == 0) {
+                            st.pos[slot] = (uint32_t)(p - base);
+                            st.len[slot] = (uint32_t)len;
+                            cur = k.key;
+                        }
+                    }
+                    if (cur == k.key) {
+                        atomicAdd(&st.cnt[slot], 1u);
+                        done = true;
+                    }
+                    slot = (slot + 1) & (COUNT_SLOTS - 1);
+                }
+            }
+            if (!done) unique_insert(P.ut, P.status, P.text, p, (uint32_t)len, k, 1);
+        }
+    }
+    __syncthreads();
+    // fold the CTA's table into the context's table
+    for (uint32_t s = threadIdx.x; s < COUNT_SLOTS; s += COUNT_THREADS) {
+        if (st.key[s] == 0) continue;
+        uint64_t p = base + st.pos[s];
+        uint32_t len = st.len[s];
+        TokenKey k = hash_bytes(P.text, p, len);  // recomputes the check word (not kept in shared memory)
+        unique_insert(P.ut, P.status, P.text, p, len, k, st.cnt[s]);
+    }
+    // total occurrences (block-reduced)
+    for (int o = 16; o; o >>= 1) local_tokens += __shfl_down_sync(0xFFFFFFFFu, local_tokens, o);
+    if ((threadIdx.x & 31) == 0 && local_tokens) atomicAdd(reinterpret_cast<unsigned long long*>(P.ut.counters + 2), (unsigned long long)local_tokens);
+}
+
+// One thread per imported pretoken: pretoken i = blob[off[i], off[i] + len[i]).
+__global__ void import_kernel(const uint8_t* __restrict__ blob, const uint64_t* __restrict__ off, const uint32_t* __restrict__ len,
+                              const uint64_t* __restrict__ cnt, uint64_t n_unique, UniqueTable ut, uint32_t* status) {
+    uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (i >= n_unique) return;
+    TokenKey k = hash_bytes(blob, off[i], len[i]);
+    unique_insert(ut, status, blob, off[i], len[i], k, cnt[i]);
+    atomicAdd(reinterpret_cast<unsigned long long*>(ut.counters + 2), (unsigned long long)cnt[i]);
+}
+
+// One thread per table slot: every occupied slot takes the next index and the next byte range.
+__global__ void export_kernel(UniqueTable ut, uint8_t* __restrict__ blob, uint64_t* __restrict__ off, uint32_t* __restrict__ len,
+                              uint64_t* __restrict__ cnt, unsigned long long* cursors /* [0] index, [1] bytes */) {
+    uint64_t slot = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (slot > ut.cap_mask || ut.key[slot] == 0) return;
+    uint32_t L = ut.len[slot];
+    uint64_t idx = atomicAdd(&cursors[0], 1ull);
+    uint64_t at = atomicAdd(&cursors[1], (unsigned long long)L);
+    const uint8_t* src = ut.pool + ut.pool_off[slot];
+    for (uint32_t k = 0; k < L; k++) blob[at + k] = src[k];
+    off[idx] = at;
+    len[idx] = L;
+    cnt[idx] = ut.cnt[slot];
+}
+
+}  // namespace
+
+int launch_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, cudaStream_t s) {
+    if (n == 0) return BPE_OK;
+    CountParams P;
+    P.text = d_text; P.n = n; P.start = d_start; P.status = ctx->d_status; P.ut = ctx->ut;
+    P.n_words = (n + 31) / 32;
+    uint64_t grid = (uint64_t)BPE_N_SM * 2;
+    // keep ranges a multiple of the CTA width so that all threads stay busy; small inputs use fewer CTAs
+    uint64_t per = (P.n_words + grid - 1) / grid;
+    per = (per + COUNT_THREADS - 1) / COUNT_THREADS * COUNT_THREADS;
+    grid = (P.n_words + per - 1) / per;
+    P.words_per_block = per;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CUDA_TRY(ctx, cudaFuncSetAttribute(count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SharedTable)));
+        attr_set = true;
+    }
+    KernelTimer t(ctx, "count_kernel", s);
+    count_kernel<<<(unsigned)grid, COUNT_THREADS, sizeof(SharedTable), s>>>(P, ctx->sp);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return BPE_OK;
+}
+
+int launch_import(bpe_ctx* ctx, const uint8_t* d_blob, const uint64_t* d_off, const uint32_t* d_len, const uint64_t* d_cnt,
+                  uint64_t n_unique, cudaStream_t s) {
+    if (!n_unique) return BPE_OK;
+    import_kernel<<<(unsigned)((n_unique + 255) / 256), 256, 0, s>>>(d_blob, d_off, d_len, d_cnt, n_unique, ctx->ut, ctx->d_status);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return BPE_OK;
+}
+
+int launch_export(bpe_ctx* ctx, uint8_t* d_blob, uint64_t* d_off, uint32_t* d_len, uint64_t* d_cnt, cudaStream_t s) {
+    unsigned long long* cursors = (unsigned long long*)ctx_scratch(ctx, 0, 2 * sizeof(unsigned long long));
+    if (!cursors) return BPE_ERR_CUDA;
+    CUDA_TRY(ctx, cudaMemsetAsync(cursors, 0, 2 * sizeof(unsigned long long), s));
+    uint64_t slots = ctx->ut.cap_mask + 1;
+    export_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, s>>>(ctx->ut, d_blob, d_off, d_len, d_cnt, cursors);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return BPE_OK;
+}

@@ -1,0 +1,153 @@
+/* bpe_b200.h — C-ABI of libbpe_b200.so: the BPE tokenizer hot path of milasd/BPE-Transformer on B200 (sm_100a).
+ *
+ * Plain C, `int` status (0 = ok), plain pointers and sizes; no torch types.  Pointers named d_* are DEVICE
+ * pointers (e.g. torch.Tensor.data_ptr()), h_* are host pointers.  `stream` is a cudaStream_t passed as
+ * void* (NULL = the legacy default stream).  One context per GPU; calls on one context must be serialised
+ * by the caller.  The library never frees caller buffers; everything it allocates belongs to the context
+ * and is released by bpe_ctx_destroy().  Every entry point returns only after its work on `stream` has
+ * completed (it synchronises the stream to read its status word), unless stated otherwise.
+ *
+ * Citations give the reference code (paths relative to the reference repo) each entry point replaces.
+ * The Python host side that mirrors the reference's own API on top of this is bpe_transformer_b200/.
+ */
+#ifndef BPE_B200_H
+#define BPE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bpe_ctx bpe_ctx;
+
+/* status codes */
+#define BPE_OK 0
+#define BPE_ERR_CUDA 1          /* a CUDA runtime call failed; see bpe_last_error() */
+#define BPE_ERR_INVALID_UTF8 2  /* the text is not valid UTF-8 (the reference decodes with errors="ignore",
+                                   pretokenization.py:194: the host side cleans the bytes and calls again) */
+#define BPE_ERR_CAPACITY 3      /* a context-owned table or pool is full; enlarge with bpe_ctx_configure() */
+#define BPE_ERR_ARGUMENT 4
+#define BPE_ERR_HASH_COLLISION 5 /* two different pretokens share a 64-bit key and differ in the 32-bit check */
+#define BPE_ERR_MISSING_ID 6    /* a merge whose joined bytes have no id was applied (reference: KeyError,
+                                   bpe_tokenizer.py:290) or a byte / special token has no id (:175, :206) */
+#define BPE_ERR_NO_PAIRS 7      /* nothing to merge (reference: AttributeError, bpe_trainer.py:237-240) */
+#define BPE_ERR_STATE 8         /* call order: e.g. bpe_encode() before bpe_load_model() */
+
+/* flags for bpe_scan() / bpe_encode() */
+#define BPE_CUT_AFTER_NEWLINE 1u /* a segment boundary after every '\n': BPETokenizer.encode_iterable over
+                                    an iterable of lines (bpe_tokenizer.py:368-379) */
+
+/* Every text buffer handed to the library must be readable for BPE_TEXT_PAD bytes past its end
+ * (contents irrelevant), and aligned to 16 bytes. */
+#define BPE_TEXT_PAD 64
+
+/* ---- context ---------------------------------------------------------------------------------------- */
+
+/* Creates a context on CUDA device `device`.  Uploads the code-point class tables (include/
+ * bpe_unicode_tables.h, generated from the `regex` module the reference scans with: pretokenization.py:2). */
+int bpe_ctx_create(int device, bpe_ctx** out);
+void bpe_ctx_destroy(bpe_ctx* ctx);
+/* Text of the last error on this context (never NULL).  With ctx == NULL: the last bpe_ctx_create() error. */
+const char* bpe_last_error(const bpe_ctx* ctx);
+
+/* Sizes of the context-owned pretoken table: 2^table_log2 slots (32 B each) and a byte pool holding one
+ * copy of every distinct pretoken.  Call before the first bpe_count(); drops any counted pretokens.
+ * Defaults: table_log2 = 22, pool_bytes = 256 MiB. */
+int bpe_ctx_configure(bpe_ctx* ctx, int table_log2, uint64_t pool_bytes);
+
+/* Special tokens, concatenated in `h_blob`, token k = h_blob[h_off[k] .. h_off[k+1]).  The ORDER is the match
+ * priority at one position; the host passes them longest first, which is what the reference's
+ * split_on_special_tokens does (pretokenization.py:228-232).  n = 0 clears them. */
+int bpe_set_special_tokens(bpe_ctx* ctx, const uint8_t* h_blob, const uint32_t* h_off, int n);
+
+/* ---- pretokenisation ---------------------------------------------------------------------------------- */
+
+/* Token-start bitmask of d_text[0, n): bit (i & 31) of d_start[i >> 5] is set iff a token starts at byte i.
+ * A token is a match of the GPT-2 split pattern (settings.py:8) as regex.finditer finds it inside one
+ * segment (pretokenization.py:238-252), or one special token; segments are what is left after the text is
+ * cut at `d_cuts` (sorted byte positions with a boundary in front of them; may be NULL) and/or after every
+ * newline (flag), and then split on the special tokens (pretokenization.py:211-235).
+ * d_start must hold n/32 + 2 words.  Returns BPE_ERR_INVALID_UTF8 if the text is not valid UTF-8. */
+int bpe_scan(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint64_t* d_cuts, uint64_t n_cuts,
+             uint32_t flags, uint32_t* d_start, void* stream);
+
+/* Adds every pretoken of d_text (given its start mask) to the context's table of distinct pretokens with
+ * occurrence counts — the Counter that pretokenize_chunk builds and parallel_pretokenization folds
+ * (pretokenization.py:73-111, 171-208).  Special tokens are left out.  Callable once per shard / chunk. */
+int bpe_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, void* stream);
+
+/* Number of distinct pretokens counted so far, the sum of their lengths, and the total occurrences. */
+int bpe_unique_stats(bpe_ctx* ctx, uint64_t* n_unique, uint64_t* n_bytes, uint64_t* n_tokens);
+
+/* Copies the table out: pretoken k = d_blob[d_off[k] .. d_off[k] + d_len[k]) with count d_cnt[k] (order
+ * unspecified).  d_blob holds n_bytes + BPE_TEXT_PAD bytes, the other arrays n_unique entries.  Used to
+ * exchange per-GPU tables (all-gather) and to hand the Counter to Python. */
+int bpe_unique_export(bpe_ctx* ctx, uint8_t* d_blob, uint64_t* d_off, uint32_t* d_len, uint64_t* d_cnt, void* stream);
+
+/* Adds pretokens (same layout as bpe_unique_export; d_blob 16-byte aligned and padded) with their counts to
+ * the table: the fold of the per-worker Counters (pretokenization.py:109), here across GPUs. */
+int bpe_unique_import(bpe_ctx* ctx, const uint8_t* d_blob, const uint64_t* d_off, const uint32_t* d_len,
+                      const uint64_t* d_cnt, uint64_t n_unique, void* stream);
+
+/* Forgets all counted pretokens (and cached encodings). */
+int bpe_unique_reset(bpe_ctx* ctx);
+
+/* ---- training ------------------------------------------------------------------------------------------ */
+
+/* Learns merges from the counted pretokens until the vocabulary holds `vocab_size` entries or no pair
+ * qualifies: BPETrainer._initialize_pairs_cache + _merge_tokens + _merge_pair + _get_adjacency_pairs
+ * (bpe_trainer.py:169-426), including its neighbour double counting and its tie-break "highest count, then
+ * the lexicographically greater (bytes, bytes) pair" (bpe_trainer.py:36-67).
+ * Initial vocabulary: ids 0..255 are the single bytes, ids 256..first_new_id-1 the special tokens, whose
+ * bytes come in h_init_blob / h_init_off (first_new_id + 1 offsets, all first_new_id tokens).
+ * Merge k creates id first_new_id + k = (h_merge_a[k], h_merge_b[k]); both arrays hold vocab_size -
+ * first_new_id entries.  *n_merges receives the number learned. */
+int bpe_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const uint8_t* h_init_blob,
+              const uint32_t* h_init_off, uint32_t* h_merge_a, uint32_t* h_merge_b, uint32_t* n_merges,
+              void* stream);
+
+/* Timing of the last bpe_train() on this context, in milliseconds of device time:
+ * out[0] word table + pair histogram, out[1] merge loop, out[2] number of loop iterations. */
+int bpe_train_timing(bpe_ctx* ctx, double out[3]);
+
+/* ---- encoding ------------------------------------------------------------------------------------------ */
+
+/* Loads a tokenizer: BPETokenizer.__init__ (bpe_tokenizer.py:38-60).  Merge r joins ids (h_a[r], h_b[r])
+ * into h_merged[r] (0xFFFFFFFF = the joined bytes have no id); rows are in priority order and are over
+ * canonical ids, i.e. the host has already resolved bytes -> id the way the reference's dicts do
+ * (:55 later duplicate wins, :85 later id wins).  h_byte_to_id[256] (0xFFFFFFFF = byte not in the vocab),
+ * h_special_id[k] = id of special token k of bpe_set_special_tokens().  Clears cached encodings. */
+int bpe_load_model(bpe_ctx* ctx, const uint32_t* h_a, const uint32_t* h_b, const uint32_t* h_merged,
+                   uint32_t n_merges, const uint32_t* h_byte_to_id, const uint32_t* h_special_id);
+
+/* BPETokenizer.encode (bpe_tokenizer.py:139-290) over d_text, segmented as bpe_scan() describes: every
+ * pretoken becomes its byte ids, merged by repeatedly joining the leftmost pair of minimum merge rank;
+ * special tokens become their id.  Ids are written in text order to d_out as uint16 (out_elem_bytes = 2)
+ * or uint32 (4); `cap` = capacity in elements; *n_out = ids produced (if > cap nothing was written and
+ * BPE_ERR_CAPACITY is returned).  d_start may be NULL (the library scans into its own scratch) or a mask
+ * made by bpe_scan() with the same cuts and flags.  Encodings of distinct pretokens stay cached in the
+ * context across calls (the reference's _encoding_cache, bpe_tokenizer.py:57-60, 232-236). */
+int bpe_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint64_t* d_cuts, uint64_t n_cuts,
+               uint32_t flags, const uint32_t* d_start, void* d_out, int out_elem_bytes, uint64_t cap,
+               uint64_t* n_out, void* stream);
+
+/* BPETokenizer.decode's byte concatenation (bpe_tokenizer.py:119-137): writes vocab[id] for every id
+ * (U+FFFD bytes EF BF BD for ids without an entry) to d_bytes; the vocabulary comes as h_vocab_blob /
+ * h_vocab_off over ids 0..n_vocab-1 (empty entry = no such id).  *n_bytes = bytes produced. */
+int bpe_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_ids, const uint8_t* h_vocab_blob,
+               const uint64_t* h_vocab_off, uint32_t n_vocab, uint8_t* d_bytes, uint64_t cap, uint64_t* n_bytes,
+               void* stream);
+
+/* Per-kernel device time of the last call on this context, for bench.py: fills up to `max` entries of
+ * (name, milliseconds, launches); returns the number of entries. */
+typedef struct { const char* name; double ms; uint64_t launches; } bpe_kernel_time;
+int bpe_kernel_times(bpe_ctx* ctx, bpe_kernel_time* out, int max);
+/* Switch per-kernel CUDA-event timing on (1) or off (0, default). */
+int bpe_set_profiling(bpe_ctx* ctx, int on);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

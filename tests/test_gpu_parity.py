@@ -1,0 +1,365 @@
+"""Parity of the CUDA path with the oracle and the reference's golden vectors — runs on a B200 (`-m gpu`).
+
+Everything here goes through the C-ABI of libbpe_b200.so (bpe_transformer_b200._lib.Engine is a thin ctypes
+wrapper: one method per exported function) or through the reference-shaped Python API on top of it.  The bar is
+bit-exact: identical start masks, Counters, ordered merges, vocab dicts and token ids.
+"""
+from __future__ import annotations
+
+import random
+from collections import Counter
+
+import numpy as np
+import pytest
+
+import bpe_ref_port as port
+import c_oracle
+from conftest import EOT, expand_row, load_golden, synth_corpus, with_specials
+
+pytestmark = pytest.mark.gpu
+
+PRETOK = load_golden("pretok.json.gz")
+TRAIN = load_golden("train.json.gz")
+ENCODE = load_golden("encode.json.gz")
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from bpe_transformer_b200 import _lib
+
+    return _lib.get_engine()
+
+
+def gpu_mask(engine, data: bytes, specials=None, cuts=None, flags=0) -> np.ndarray:
+    from bpe_transformer_b200 import _lib
+
+    engine.set_special_tokens(_lib.sort_specials(specials))
+    d_text, n = engine.to_device(data)
+    mask = engine.scan(d_text, n, cuts=cuts, flags=flags)
+    return mask.cpu().numpy().view(np.uint32)[:(n + 31) // 32]
+
+
+def gpu_counter(engine, data: bytes, specials=None, cuts=None, flags=0) -> Counter:
+    from bpe_transformer_b200 import _lib
+    from bpe_transformer_b200.tokenization.preprocessing.pretokenization import counter_from_engine
+
+    engine.set_special_tokens(_lib.sort_specials(specials))
+    engine.unique_reset()
+    d_text, n = engine.to_device(data)
+    engine.count(d_text, n, engine.scan(d_text, n, cuts=cuts, flags=flags))
+    return counter_from_engine(engine)
+
+
+def first_diff(a: np.ndarray, b: np.ndarray, data: bytes) -> str:
+    bad = np.flatnonzero(a != b)
+    if not len(bad):
+        return ""
+    w = int(bad[0])
+    lo = max(0, w * 32 - 24)
+    return f"word {w}: gpu {int(a[w]):032b} oracle {int(b[w]):032b} text {data[lo:w * 32 + 40]!r}"
+
+
+# ---- scan ---------------------------------------------------------------------------------------------------
+ALPHABET = [" ", " ", "  ", "\n", "\t", "'", "'s", "'ll", "'ve", "'re", "'d", "'m", "'t", "a", "b", "s", "l", "v", "e", "r",
+            "L", "1", "23", ".", "!", "?", "é", "ü", " ", "　", " ", "你", "好", "٣", "½", "🙃", "x", "\r", "-", "_",
+            "\x1c", "\x85", " ", " ", "ǅ", "ʰ", "़", "​", "Ⅷ", "<|endoftext|>", "<|", "<", "|>"]
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+@pytest.mark.parametrize("specials", [[], [EOT], [EOT, EOT + EOT, "<|"]])
+def test_scan_fuzz_matches_oracle(engine, seed, specials):
+    """Many short random strings in one buffer, separated by caller cuts (every string is its own piece)."""
+    rnd = random.Random(seed)
+    pieces, cuts, total = [], [], 0
+    for _ in range(4000):
+        s = "".join(rnd.choice(ALPHABET) for _ in range(rnd.randint(1, 40))).encode("utf-8")
+        pieces.append(s)
+        total += len(s)
+        cuts.append(total)
+    data = b"".join(pieces)
+    want = c_oracle.scan(data, specials, cuts[:-1])
+    got = gpu_mask(engine, data, specials, cuts[:-1])
+    assert np.array_equal(got, want), first_diff(got, want, data)
+    # and as one long piece, and cut after newlines
+    for flags in (0, c_oracle.CUT_AFTER_NEWLINE):
+        want = c_oracle.scan(data, specials, None, flags)
+        got = gpu_mask(engine, data, specials, None, flags)
+        assert np.array_equal(got, want), first_diff(got, want, data)
+
+
+@pytest.mark.parametrize("key", ["corpus.en", "german.txt", "tinystories_sample.txt", "inline:scripts", "inline:whitespace",
+                                 "inline:contractions", "synth:owt:4:300000", "synth:ts:5:300000", "synth:owt:3:2000000"])
+def test_scan_texts_match_oracle(engine, input_bytes, key):
+    data = input_bytes(key)
+    for specials in ([], [EOT]):
+        for flags in (0, c_oracle.CUT_AFTER_NEWLINE):
+            want = c_oracle.scan(data, specials, None, flags)
+            got = gpu_mask(engine, data, specials, None, flags)
+            assert np.array_equal(got, want), first_diff(got, want, data)
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 63, 64, 65, 8191, 8192, 8193, 16384 + 5])
+def test_scan_edge_sizes(engine, n):
+    """Empty and ragged sizes around the 32-byte chunk and the 8 KiB tile."""
+    data = synth_corpus(1, 77, 40000)[:n]
+    while data and (data[-1] & 0xC0) == 0x80:
+        data = data[:-1]
+    if data and data[-1] >= 0xC0:
+        data = data[:-1]
+    if not data:
+        assert gpu_mask(engine, data).size == 0
+        return
+    want = c_oracle.scan(data, [EOT])
+    got = gpu_mask(engine, data, [EOT])
+    assert np.array_equal(got, want), first_diff(got, want, data)
+
+
+def test_scan_long_runs_and_tile_borders(engine):
+    """Tokens far longer than a tile, specials and contractions sitting on chunk / tile borders."""
+    parts = [b"a" * 20000, b" " * 9000, b"x", b"-" * 8190, EOT.encode(), b"'ll" * 3000, ("é" * 5000).encode(), b"\n" * 8193, b"7" * 100]
+    data = b"".join(parts)
+    for shift in range(0, 40, 7):
+        d = b"z" * shift + data
+        want = c_oracle.scan(d, [EOT])
+        got = gpu_mask(engine, d, [EOT])
+        assert np.array_equal(got, want), first_diff(got, want, d)
+
+
+def test_scan_reports_invalid_utf8(engine):
+    from bpe_transformer_b200 import _lib
+
+    for bad in (b"abc \xff def", b"abc \xed\xa0\x80 def", b"abc \xe4\xbd", b"\x80abc", b"abc\xc0\xaf"):
+        with pytest.raises(_lib.InvalidUtf8):
+            gpu_mask(engine, bad * 3)
+
+
+# ---- count --------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", PRETOK, ids=lambda c: f"{c['input']}-{len(c['specials'])}sp")
+def test_counts_match_reference_golden(engine, case, input_bytes, tmp_file):
+    from bpe_transformer_b200.tokenization.preprocessing import parallel_pretokenization
+
+    data = input_bytes(case["input"])
+    want = Counter({tuple(bytes.fromhex(h)): c for h, c in case["counts"]})
+    if case["specials"] or case["n_workers"] == 1:
+        assert gpu_counter(engine, data, case["specials"]) == want
+    if case["n_workers"] <= 4:  # cpu_count() clamps n_workers; the box has more than 4 cores
+        got = parallel_pretokenization(file_path=tmp_file(data), n_workers=case["n_workers"], special_tokens=case["specials"])
+        assert got == want
+
+
+@pytest.mark.parametrize("style,seed,size", [(0, 11, 8_000_000), (1, 12, 8_000_000)])
+def test_counts_match_oracle_synthetic(engine, style, seed, size):
+    data = synth_corpus(style, seed, size)
+    assert gpu_counter(engine, data, [EOT]) == c_oracle.count(data, [EOT])
+
+
+def test_count_accumulates_over_shards(engine):
+    """bpe_count per shard (cut at special-token starts) == one call over the whole text."""
+    data = synth_corpus(0, 21, 3_000_000)
+    whole = gpu_counter(engine, data, [EOT])
+    from bpe_transformer_b200 import _lib
+    from bpe_transformer_b200.tokenization.preprocessing.pretokenization import counter_from_engine
+
+    engine.set_special_tokens(_lib.sort_specials([EOT]))
+    engine.unique_reset()
+    cuts = [0]
+    for k in range(1, 5):
+        cuts.append(data.index(EOT.encode(), k * len(data) // 5))
+    cuts.append(len(data))
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        d_text, n = engine.to_device(data[a:b])
+        engine.count(d_text, n, engine.scan(d_text, n))
+    assert counter_from_engine(engine) == whole
+    # export -> import into a fresh table doubles every count
+    blob, off, ln, cnt = engine.unique_export()
+    engine.unique_import(blob, off, ln, cnt)
+    doubled = counter_from_engine(engine)
+    assert doubled == Counter({k: 2 * v for k, v in whole.items()})
+
+
+# ---- train --------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", TRAIN, ids=lambda c: f"{c['input']}-{c['vocab_size']}")
+def test_train_matches_reference_golden(case, input_bytes, tmp_file):
+    from bpe_transformer_b200.tokenization import BPETrainer
+    from adapters import run_train_bpe
+
+    data = input_bytes(case["input"])
+    want_merges = [(bytes.fromhex(a), bytes.fromhex(b)) for a, b in case["merges"]]
+    want_vocab = {int(k): bytes.fromhex(v) for k, v in case["vocab"].items()}
+    path = tmp_file(data)
+    if case["n_workers"] is None:
+        vocab, merges = run_train_bpe(path, case["vocab_size"], case["specials"])
+    else:
+        tr = BPETrainer(vocab_size=case["vocab_size"], special_tokens=case["specials"])
+        tr.train(input_path=path, n_workers=case["n_workers"])
+        vocab, merges = tr.vocab, tr.merges
+    bad = next((i for i, (x, y) in enumerate(zip(merges, want_merges)) if x != y), None)
+    assert bad is None, f"merge {bad}: gpu {merges[bad]} reference {want_merges[bad]}"
+    assert merges == want_merges
+    assert vocab == want_vocab
+
+
+def test_train_course_golden_c1(input_bytes, tmp_file):
+    """BASELINE config 1: the reference's own test (tests/test_train_bpe.py:27-63)."""
+    from adapters import run_train_bpe
+
+    g = load_golden("course_golden.json.gz")
+    vocab, merges = run_train_bpe(tmp_file(input_bytes("corpus.en")), 500, [EOT])
+    assert merges == [(bytes.fromhex(a), bytes.fromhex(b)) for a, b in g["merges"]]
+    assert set(vocab.keys()) == {int(k) for k in g["vocab"]}
+    assert set(vocab.values()) == {bytes.fromhex(v) for v in g["vocab"].values()}
+
+
+@pytest.mark.parametrize("style,seed,size,vocab_size", [(0, 31, 4_000_000, 3000), (1, 32, 1_500_000, 1200)])
+def test_train_matches_port_on_fresh_corpus(style, seed, size, vocab_size, tmp_path):
+    from adapters import run_train_bpe
+
+    path = synth_corpus(style, seed, size, str(tmp_path / "c.txt"))
+    words = port.count_pretokens(path, 8, [EOT])
+    want_vocab, want_merges = port.train_from_counts(words, vocab_size, [EOT])
+    vocab, merges = run_train_bpe(path, vocab_size, [EOT])
+    bad = next((i for i, (x, y) in enumerate(zip(merges, want_merges)) if x != y), None)
+    assert bad is None, f"merge {bad}: gpu {merges[bad]} port {want_merges[bad]}"
+    assert (vocab, merges) == (want_vocab, want_merges)
+
+
+def test_train_ignores_invalid_utf8_like_the_reference(tmp_file):
+    """pretokenization.py:194 decodes with errors="ignore"."""
+    from adapters import run_train_bpe
+
+    data = synth_corpus(0, 41, 200_000)
+    dirty = data[:1000] + b"\xff\xfe" + data[1000:50_000] + b"\xe4\xbd" + data[50_000:]
+    path = tmp_file(dirty)
+    want = port.train_from_counts(port.count_pretokens(path, 4, [EOT]), 600, [EOT])
+    assert run_train_bpe(path, 600, [EOT]) == want
+
+
+def test_train_error_conventions(tmp_file):
+    from bpe_transformer_b200 import train_bpe
+    from bpe_transformer_b200.tokenization import BPETrainer
+
+    with pytest.raises(ValueError):
+        train_bpe(tmp_file(b"abc"), 200, [EOT])  # main.py:12-13
+    with pytest.raises(ValueError):
+        BPETrainer(vocab_size=100)  # bpe_trainer.py:82-83
+    with pytest.raises(AttributeError):
+        train_bpe(tmp_file(b"a b c"), 300, [EOT])  # single-byte pretokens only: no pairs (:237-240)
+    with pytest.raises(AttributeError):
+        train_bpe(tmp_file(b""), 300, [EOT])
+    with pytest.raises(FileNotFoundError):
+        train_bpe("/nonexistent/corpus.txt", 300, [EOT])
+    vocab, merges = train_bpe(tmp_file(b"ab ab ab"), 257, [EOT])  # room for nothing: initial vocab comes back
+    assert len(vocab) == 257 and merges == []
+
+
+def test_save_and_load_roundtrip(tmp_path, input_bytes, tmp_file):
+    from bpe_transformer_b200.tokenization import BPETokenizer, BPETrainer
+
+    tr = BPETrainer(vocab_size=400, special_tokens=[EOT])
+    tr.train(input_path=tmp_file(input_bytes("tinystories_sample.txt")), n_workers=2)
+    tr.save_trainer(output_dir=tmp_path / "tok")
+    tok = BPETokenizer.from_files(tmp_path / "tok" / "vocab.pkl", tmp_path / "tok" / "merges.pkl", special_tokens=[EOT])
+    assert tok.vocab == tr.vocab and tok.merges == tr.merges
+    text = input_bytes("tinystories_sample.txt").decode()
+    assert tok.decode(tok.encode(text)) == text
+
+
+# ---- encode -------------------------------------------------------------------------------------------------
+def _models(gpt2_model, ts10k_model):
+    return {"gpt2": gpt2_model, "ts10k": ts10k_model}
+
+
+@pytest.mark.parametrize("row", ENCODE, ids=lambda r: f"{r['model']}-{r['input']}")
+def test_encode_matches_reference_golden(row, input_bytes, gpt2_model, ts10k_model, tmp_file):
+    from adapters import get_tokenizer
+
+    vocab, merges = _models(gpt2_model, ts10k_model)[row["model"]]
+    tok = get_tokenizer(with_specials(vocab, row["specials"]), merges, row["specials"])
+    data = input_bytes(row["input"])
+    text = data.decode("utf-8")
+    want = expand_row(row, "encode")
+    got = tok.encode(text)
+    bad = next((i for i, (x, y) in enumerate(zip(got, want)) if x != y), None)
+    assert bad is None and len(got) == len(want), f"id {bad}: gpu {got[bad:bad + 5] if bad is not None else len(got)} reference {want[bad:bad + 5] if bad is not None else len(want)}"
+    assert tok.decode(got) == text
+    with open(tmp_file(data)) as fh:  # a file handle: an iterable of lines
+        assert list(tok.encode_iterable(fh)) == expand_row(row, "iterable_lines")
+    translated = text.replace("\r\n", "\n").replace("\r", "\n")
+    assert list(tok.encode_iterable(translated.splitlines(keepends=True))) == expand_row(row, "iterable_lines")
+    chunks = [text[i:i + 997] for i in range(0, len(text), 997)]
+    assert list(tok.encode_iterable(chunks)) == expand_row(row, "iterable_chunks_997")
+    if len(data) < 50_000:
+        assert tok.decode_array(np.asarray(want)) == b"".join(tok.vocab[i] for i in want)
+
+
+@pytest.mark.parametrize("model", ["gpt2", "ts10k"])
+@pytest.mark.parametrize("style,seed", [(0, 51), (1, 52)])
+def test_encode_matches_oracle_synthetic(model, style, seed, gpt2_model, ts10k_model, tmp_path):
+    from adapters import get_tokenizer
+
+    vocab, merges = _models(gpt2_model, ts10k_model)[model]
+    vocab = with_specials(vocab, [EOT])
+    path = synth_corpus(style, seed, 3_000_000, str(tmp_path / "c.txt"))
+    data = open(path, "rb").read()
+    tok = get_tokenizer(vocab, merges, [EOT])
+    ct = c_oracle.COracleTokenizer(vocab, merges, [EOT])
+    want = np.asarray(ct.encode_lines(data.decode()), dtype=np.uint32)
+    got = tok.encode_file_to_array(path)
+    assert got.dtype == np.uint16
+    assert np.array_equal(got.astype(np.uint32), want)
+    want_whole = ct.encode(data.decode())
+    assert tok.encode(data.decode()) == want_whole
+    assert tok.decode_array(got) == data
+
+
+def test_encode_with_a_freshly_trained_vocab(tmp_path):
+    """train on the GPU, encode with the result, check both against the port."""
+    from adapters import get_tokenizer, run_train_bpe
+
+    path = synth_corpus(0, 61, 2_000_000, str(tmp_path / "c.txt"))
+    vocab, merges = run_train_bpe(path, 2000, [EOT])
+    text = open(path, encoding="utf-8").read()[:300_000]
+    tok = get_tokenizer(vocab, merges, [EOT])
+    assert tok.encode(text) == port.PortTokenizer(vocab, merges, [EOT]).encode(text)
+
+
+def test_encode_error_conventions(gpt2_model):
+    from adapters import get_tokenizer
+
+    vocab, merges = gpt2_model
+    tok = get_tokenizer(dict(vocab), merges, ["<|missing|>"])  # special token without an id: KeyError when met (:175)
+    assert tok.encode("no special here") == get_tokenizer(dict(vocab), merges, None).encode("no special here")
+    with pytest.raises(KeyError):
+        tok.encode("a <|missing|> b")
+    small = {k: v for k, v in vocab.items() if v != b"z"}
+    with pytest.raises(KeyError):
+        get_tokenizer(small, merges, None).encode("zebra")  # byte without an id (:206)
+    assert get_tokenizer(dict(vocab), merges, None).decode([0, 10**9, 1]) == port.PortTokenizer(vocab, merges).decode([0, 10**9, 1])
+
+
+def test_large_roundtrip_and_conservation(tmp_path, ts10k_model):
+    """Size-independent properties on a larger corpus (256 MB): occurrences == start bits outside specials,
+    decode(encode(x)) == x through the GPU decoder, ids below the vocab size."""
+    from adapters import get_tokenizer
+    from bpe_transformer_b200 import _lib
+
+    path = synth_corpus(0, 71, 256_000_000, str(tmp_path / "big.txt"))
+    data = open(path, "rb").read()
+    eng = _lib.get_engine()
+    eng.set_special_tokens(_lib.sort_specials([EOT]))
+    eng.unique_reset()
+    d_text, n = eng.to_device(data)
+    mask = eng.scan(d_text, n)
+    eng.count(d_text, n, mask)
+    n_unique, n_bytes, n_tokens = eng.unique_stats()
+    bits = int(np.unpackbits(mask.cpu().numpy().view(np.uint8)).sum())
+    assert n_tokens == bits - data.count(EOT.encode())
+    vocab, merges = ts10k_model
+    tok = get_tokenizer(with_specials(vocab, [EOT]), merges, [EOT])
+    ids = tok.encode_file_to_array(path)
+    assert int(ids.max()) < len(tok.vocab)
+    assert tok.decode_array(ids) == data
+    # the first 2 MB against the C oracle (cut at a line end)
+    cut = data.rindex(b"\n", 0, 2_000_000) + 1
+    want = c_oracle.COracleTokenizer(tok.vocab, merges, [EOT]).encode_lines(data[:cut].decode())
+    assert ids[:len(want)].tolist() == want
