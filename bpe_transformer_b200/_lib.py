@@ -9,6 +9,7 @@ import ctypes as C
 import os
 import pathlib
 import threading
+import warnings
 
 import numpy as np
 
@@ -162,7 +163,9 @@ class Engine:
         if isinstance(data, torch.Tensor):
             host = data
         else:
-            host = torch.frombuffer(memoryview(data), dtype=torch.uint8) if len(data) else torch.empty(0, dtype=torch.uint8)
+            with warnings.catch_warnings():  # bytes are read-only; the tensor is only ever a copy source
+                warnings.simplefilter("ignore", UserWarning)
+                host = torch.frombuffer(memoryview(data), dtype=torch.uint8) if len(data) else torch.empty(0, dtype=torch.uint8)
         n = int(host.numel())
         dev = torch.empty(n + TEXT_PAD, dtype=torch.uint8, device=f"cuda:{self.device}")
         if n:

@@ -319,7 +319,7 @@ int bpe_kernel_times(bpe_ctx* ctx, bpe_kernel_time* out, int max) {
 
 int bpe_set_profiling(bpe_ctx* ctx, int on) {
     if (!ctx) return BPE_ERR_ARGUMENT;
-    ctx->profiling = on != 0;
+    ctx->profiling = on != 0;  // on: CUDA-event timing per launch; either way the launch counters restart
     ctx->times.clear();
     return BPE_OK;
 }

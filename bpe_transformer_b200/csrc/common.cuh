@@ -240,7 +240,8 @@ uint32_t ctx_read_status(bpe_ctx* ctx, cudaStream_t s, bool clear = true);
         if (e__ != cudaSuccess) return ctx_fail((ctx), BPE_ERR_CUDA, #expr, e__); \
     } while (0)
 
-// RAII CUDA-event timer that appends to ctx->times when profiling is on.
+// RAII launch record: always counts the launch under `name`; with profiling on it also brackets the launch
+// with CUDA events on the launching stream and accumulates the device time.
 struct KernelTimer {
     bpe_ctx* ctx;
     const char* name;
@@ -254,18 +255,17 @@ struct KernelTimer {
         }
     }
     ~KernelTimer() {
+        float ms = 0;
         if (a) {
             cudaEventRecord(b, s);
             cudaEventSynchronize(b);
-            float ms = 0;
             cudaEventElapsedTime(&ms, a, b);
-            bool found = false;
-            for (auto& t : ctx->times)
-                if (t.name == name) { t.ms += ms; t.launches++; found = true; }
-            if (!found) ctx->times.push_back({name, (double)ms, 1});
             cudaEventDestroy(a);
             cudaEventDestroy(b);
         }
+        for (auto& t : ctx->times)
+            if (t.name == name) { t.ms += ms; t.launches++; return; }
+        ctx->times.push_back({name, (double)ms, 1});
     }
 };
 

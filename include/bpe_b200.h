@@ -140,11 +140,12 @@ int bpe_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_id
                const uint64_t* h_vocab_off, uint32_t n_vocab, uint8_t* d_bytes, uint64_t cap, uint64_t* n_bytes,
                void* stream);
 
-/* Per-kernel device time of the last call on this context, for bench.py: fills up to `max` entries of
- * (name, milliseconds, launches); returns the number of entries. */
+/* Kernels launched on this context since the last bpe_set_profiling(): fills up to `max` entries of
+ * (name, milliseconds, launches); returns the number of entries.  Launches are always counted; milliseconds
+ * (CUDA events on the launching stream) only while profiling is on. */
 typedef struct { const char* name; double ms; uint64_t launches; } bpe_kernel_time;
 int bpe_kernel_times(bpe_ctx* ctx, bpe_kernel_time* out, int max);
-/* Switch per-kernel CUDA-event timing on (1) or off (0, default). */
+/* Switch per-kernel CUDA-event timing on (1) or off (0, default) and restart the counters. */
 int bpe_set_profiling(bpe_ctx* ctx, int on);
 
 #ifdef __cplusplus

@@ -243,7 +243,7 @@ def test_train_error_conventions(tmp_file):
     with pytest.raises(ValueError):
         BPETrainer(vocab_size=100)  # bpe_trainer.py:82-83
     with pytest.raises(AttributeError):
-        train_bpe(tmp_file(b"a b c"), 300, [EOT])  # single-byte pretokens only: no pairs (:237-240)
+        train_bpe(tmp_file(b"a\nb\nc"), 300, [EOT])  # single-byte pretokens only: no pairs (:237-240)
     with pytest.raises(AttributeError):
         train_bpe(tmp_file(b""), 300, [EOT])
     with pytest.raises(FileNotFoundError):
