@@ -1,0 +1,449 @@
+#!/usr/bin/env python3
+"""bench.py — BASELINE.json's metric on B200: train_bpe seconds (10k vocab, 2.1 GB synthetic TinyStories-shaped
+corpus) and encode GB/s, next to the reference's CPU path timed on the same box.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--bytes B] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+One JSON line on stdout (rank 0).  A "step" is one full pass of the training hot path over the corpus:
+token-start scan -> distinct-pretoken count -> (N > 1: all-gather of the tables) -> pair histogram -> merge loop.
+  value      seconds per step with the corpus already resident in HBM (CUDA events, max over ranks)
+  e2e        seconds per call of the public API train_bpe(path, 10000, ["<|endoftext|>"]) — file -> pinned host
+             memory -> HBM -> kernels -> merges back on the host, all inside the timed region
+  encode     the second half of the metric: GB/s of corpus through BPETokenizer (resident and end to end)
+  roofline   the slower of the two HBM-bound kernels of a step (scan / count): algorithmic bytes = corpus bytes
+  cpu_baseline  oracle/bpe_ref_port.py (the reference's algorithm, regex + Counter + heap, all host cores) on a
+             bounded sample, extrapolated to the workload
+The corpus (2.1 GB) is far larger than L2 (126 MB), so no L2 flush is needed between iterations.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import pathlib
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = pathlib.Path(__file__).resolve().parent
+for p in (str(ROOT), str(ROOT / "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+EOT = "<|endoftext|>"
+VOCAB_SIZE = 10_000
+METRIC = "train_bpe_seconds_10k_vocab_2.1GB"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def corpus_path(nbytes: int, seed: int = 0) -> str:
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else "/tmp"
+    return f"{base}/bpe_b200_ts_seed{seed}_{nbytes}.txt"
+
+
+def make_corpus(path: str, nbytes: int, seed: int = 0) -> None:
+    if os.path.exists(path) and os.path.getsize(path) >= nbytes:
+        return
+    so = ROOT / "tools" / "libgencorpus.so"
+    if not so.exists():
+        subprocess.check_call(["gcc", "-O2", "-shared", "-fPIC", "-pthread", "-o", str(so), str(ROOT / "tools" / "gen_corpus.c")])
+    lib = ctypes.CDLL(str(so))
+    lib.gen_corpus.restype = ctypes.c_uint64
+    tmp = path + ".tmp"
+    n = lib.gen_corpus(ctypes.c_int(0), ctypes.c_uint64(seed), ctypes.c_uint64(nbytes), tmp.encode(), ctypes.c_int(min(32, os.cpu_count() or 1)))
+    if not n:
+        raise RuntimeError("corpus generation failed")
+    os.replace(tmp, path)
+
+
+def cut_sample(path: str, nbytes: int, out: str) -> int:
+    """First ~nbytes of the corpus, cut at a document end."""
+    with open(path, "rb") as fh:
+        data = fh.read(nbytes + 65536)
+    end = data.find(EOT.encode(), nbytes)
+    end = len(data) if end < 0 else end + len(EOT) + 1
+    with open(out, "wb") as fh:
+        fh.write(data[:end])
+    return end
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU side: the reference's algorithm (port), all host cores
+# ---------------------------------------------------------------------------------------------------------
+def cpu_train_sample(path: str, total_bytes: int, sample_bytes: int) -> dict:
+    import bpe_ref_port as port
+
+    cores = os.cpu_count() or 1
+    sample = path + f".sample{sample_bytes}"
+    n_sample = cut_sample(path, sample_bytes, sample)
+    t0 = time.perf_counter()
+    words = port.count_pretokens(sample, cores, [EOT])
+    t_pre = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    _, merges = port.train_from_counts(words, VOCAB_SIZE, [EOT])
+    t_merge = time.perf_counter() - t0
+    os.unlink(sample)
+    est = t_pre * total_bytes / n_sample + t_merge
+    return {"value": est, "unit": "s", "cores": cores, "kind": "port",
+            "sample": f"first {n_sample} B of the corpus: pretokenize+count on {cores} processes {t_pre:.2f} s (scaled x{total_bytes / n_sample:.1f}), "
+                      f"merge loop to {len(merges)} merges on the sample's Counter {t_merge:.2f} s (not scaled: a lower bound, the full corpus has more distinct pretokens)",
+            "pretokenize_s_sample": t_pre, "merge_s_sample": t_merge, "sample_bytes": n_sample}
+
+
+def cpu_encode_sample(path: str, vocab, merges, sample_bytes: int) -> dict:
+    import bpe_ref_port as port
+
+    sample = path + f".encsample{sample_bytes}"
+    n_sample = cut_sample(path, sample_bytes, sample)
+    tok = port.PortTokenizer(vocab, merges, [EOT])
+    t0 = time.perf_counter()
+    n_ids = 0
+    with open(sample, encoding="utf-8") as fh:
+        for _ in tok.encode_iterable(fh):
+            n_ids += 1
+    dt = time.perf_counter() - t0
+    os.unlink(sample)
+    return {"value": n_sample / dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+            "sample": f"encode_iterable (serial: the reference's parallel variant is slower, SURVEY.md §6.2) over the first {n_sample} B, {n_ids} ids in {dt:.2f} s"}
+
+
+def run_reference(args, rank: int, world: int) -> None:
+    """--impl reference: the reference's own CPU implementation of the path (the port: the reference is pure
+    Python and /root/reference does not travel), all host cores, same metric / unit / config."""
+    if rank != 0:
+        return
+    path = corpus_path(args.bytes)
+    make_corpus(path, args.bytes)
+    total = os.path.getsize(path)
+    sample_bytes = min(total, args.cpu_sample_bytes)
+    runs = []
+    for i in range(args.warmup + args.steps):
+        r = cpu_train_sample(path, total, sample_bytes)
+        if i >= args.warmup:
+            runs.append(r)
+        log(f"[reference] step {i}: {r['value']:.1f} s estimated ({r['pretokenize_s_sample']:.2f} + {r['merge_s_sample']:.2f} s on the sample)")
+    value = sum(r["value"] for r in runs) / len(runs)
+    base = runs[-1]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": value * 1e3, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": workload_config(total, world),
+        "cpu_baseline": {"value": value, "unit": "s", "cores": base["cores"], "kind": "port", "sample": base["sample"]},
+        "e2e": {"value": value, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(total: int, world: int) -> dict:
+    return {"workload": f"BASELINE configs[1]{'/[2]' if world > 1 else ''}: train_bpe on synthetic TinyStories-shaped corpus "
+                        f"(tools/gen_corpus.c style 0 seed 0, {total} B), vocab_size=10000, special_tokens=['<|endoftext|>']; "
+                        f"encode = configs[3] over the same corpus to uint16",
+            "corpus_bytes": total, "vocab_size": VOCAB_SIZE, "sharding": f"{world} shard(s) cut at <|endoftext|> starts",
+            "l2": "inputs (2.1 GB) larger than L2 (126 MB); no flush between iterations"}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows: list[list[str]] = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        sm, mx, reasons = [], 0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx = max(mx, float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, cell in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if cell.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# GPU side
+# ---------------------------------------------------------------------------------------------------------
+def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as entry
+
+    if rank == 0:
+        entry.build()
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.barrier()
+
+    from bpe_transformer_b200 import _lib, train_bpe
+    from bpe_transformer_b200 import distributed as D
+    from bpe_transformer_b200.tokenization import BPETokenizer, BPETrainer
+    from bpe_transformer_b200.tokenization.preprocessing.pretokenization import read_file_pinned
+
+    path = corpus_path(args.bytes)
+    if rank == 0:
+        t0 = time.perf_counter()
+        make_corpus(path, args.bytes)
+        log(f"[bench] corpus {path}: {os.path.getsize(path)} B ({time.perf_counter() - t0:.1f} s)")
+    if world > 1:
+        dist.barrier()
+    total = os.path.getsize(path)
+    eng = _lib.get_engine(local_rank)
+    dev = f"cuda:{local_rank}"
+    specials = [EOT]
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- this rank's shard, resident in HBM ------------------------------------------------------------------
+    offs = D.shard_offsets(path, world, specials) if world > 1 else [0, total]
+    lo, hi = offs[rank], offs[rank + 1]
+    if world == 1:
+        host = read_file_pinned(path)
+    else:
+        host = torch.empty(hi - lo, dtype=torch.uint8, pin_memory=True)
+        with open(path, "rb", buffering=0) as fh:
+            fh.seek(lo)
+            view, got = memoryview(host.numpy()), 0
+            while got < hi - lo:
+                got += fh.readinto(view[got:])
+    d_text, n_local = eng.to_device(host)
+    torch.cuda.synchronize()
+    eng.set_special_tokens(_lib.sort_specials(specials))
+
+    result = {}
+
+    def train_step_resident():
+        eng.unique_reset()
+        mask = eng.scan(d_text, n_local)
+        eng.count(d_text, n_local, mask)
+        if world > 1:
+            D.exchange_unique(eng)
+        tr = BPETrainer(vocab_size=VOCAB_SIZE, special_tokens=specials)
+        tr._merge_tokens(eng)
+        result["trainer"] = tr
+
+    for _ in range(args.warmup):
+        train_step_resident()
+    eng.set_profiling(False)  # restart the launch counters
+    sampler = ClockSampler(local_rank)
+    sync_all()
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        train_step_resident()
+    ev1.record()
+    sync_all()
+    step_ms = max_over_ranks(ev0.elapsed_time(ev1) / args.steps)
+    launches = sum(v[1] for v in eng.kernel_times().values())
+    tr = result["trainer"]
+    timing = tr.last_timing
+    n_unique, n_unique_bytes, n_tokens = eng.unique_stats()
+    log(f"[bench] train resident: {step_ms:.1f} ms/step, {len(tr.merges)} merges, {n_unique} distinct pretokens, "
+        f"merge loop {timing['merge_loop_ms']:.1f} ms / {timing['iterations']} iterations")
+
+    # ---- end to end through the public API ---------------------------------------------------------------------
+    def train_e2e():
+        if world == 1:
+            return train_bpe(path, VOCAB_SIZE, specials)
+        return D.train_bpe_sharded(path, VOCAB_SIZE, specials)
+
+    train_e2e()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        vocab, merges = train_e2e()
+    sync_all()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+    assert merges == tr.merges
+    log(f"[bench] train end to end: {e2e_s:.3f} s/call")
+
+    # ---- encode: configs[3] ------------------------------------------------------------------------------------
+    tok = BPETokenizer(vocab, merges, specials)
+    line_offs = D.line_shard_offsets(path, world)
+    if world > 1:
+        # encode shards are cut at line ends, not at document ends: reload this rank's lines
+        llo, lhi = line_offs[rank], line_offs[rank + 1]
+        host_e = torch.empty(lhi - llo, dtype=torch.uint8, pin_memory=True)
+        with open(path, "rb", buffering=0) as fh:
+            fh.seek(llo)
+            view, got = memoryview(host_e.numpy()), 0
+            while got < lhi - llo:
+                got += fh.readinto(view[got:])
+        d_enc, n_enc = eng.to_device(host_e)
+    else:
+        d_enc, n_enc = d_text, n_local
+    torch.cuda.synchronize()
+    ids = None
+    for _ in range(args.warmup):
+        ids = tok.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=eng, on_device=(d_enc, n_enc))
+    sync_all()
+    ev0.record()
+    for _ in range(args.steps):
+        ids = tok.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=eng, on_device=(d_enc, n_enc))
+    ev1.record()
+    sync_all()
+    enc_ms = max_over_ranks(ev0.elapsed_time(ev1) / args.steps)
+    n_ids_local = int(ids.numel())
+    # roundtrip at full size: GPU decode of the ids must give back the bytes
+    back = tok.decode_array(ids, engine=eng, to_host=False) if n_enc else d_enc[:0]
+    roundtrip_ok = bool(back.numel() == n_enc and torch.equal(back, d_enc[:n_enc]))
+    del back
+
+    def encode_e2e():
+        if world == 1:
+            return tok.encode_file_to_array(path, engine=eng)
+        return D.encode_file_sharded(tok, path)[0]
+
+    encode_e2e()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        arr = encode_e2e()
+    sync_all()
+    enc_e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+    n_ids_total = n_ids_local
+    if world > 1:
+        t = torch.tensor([n_ids_local], dtype=torch.int64, device=dev)
+        dist.all_reduce(t)
+        n_ids_total = int(t.item())
+    log(f"[bench] encode: resident {total / enc_ms / 1e6:.2f} GB/s, end to end {total / enc_e2e_s / 1e9:.2f} GB/s, {n_ids_total} ids, roundtrip {roundtrip_ok}")
+
+    # ---- per-kernel device time (separate pass, CUDA events around every launch) ---------------------------------
+    eng.set_profiling(True)
+    train_step_resident()
+    k_train = eng.kernel_times()
+    eng.set_profiling(True)
+    tok.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=eng, on_device=(d_enc, n_enc))
+    k_enc = eng.kernel_times()
+    eng.set_profiling(False)
+    clocks = sampler.stop() if rank == 0 else {}
+
+    peaks_file = ROOT / "MEASURED_PEAKS.json"
+    if peaks_file.exists():
+        peak, peak_src = float(json.loads(peaks_file.read_text())["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    else:
+        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+
+    def gbps(nbytes, ms):
+        return nbytes / ms / 1e6 if ms else None
+
+    kernels = {}
+    for name, (ms, n) in k_train.items():
+        kernels[name] = {"ms": ms, "launches": n}
+    for name, (ms, n) in k_enc.items():
+        kernels["encode:" + name] = {"ms": ms, "launches": n}
+    hbm_kernels = {k: gbps(n_local, k_train[k][0]) for k in ("scan_kernel", "count_kernel") if k in k_train and k_train[k][0]}
+    dominant = min(hbm_kernels, key=hbm_kernels.get) if hbm_kernels else None
+    roofline = None
+    if dominant:
+        roofline = {"kernel": dominant, "bound": "hbm", "achieved": hbm_kernels[dominant], "peak": peak, "unit": "GB/s",
+                    "frac": hbm_kernels[dominant] / peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": n_local,
+                    "others": {k: {"achieved": v, "frac": v / peak} for k, v in hbm_kernels.items() if k != dominant}}
+
+    line = {
+        "metric": METRIC, "value": step_ms / 1e3, "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": step_ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": workload_config(total, world),
+        "e2e": {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": int(n_local), "d2h_bytes_per_step": int(8 * len(merges) + 64),
+                "api": "bpe_transformer_b200.train_bpe(path, 10000, ['<|endoftext|>'])" if world == 1 else "bpe_transformer_b200.distributed.train_bpe_sharded"},
+        "gpu_launches": int(launches),
+        "roofline": roofline,
+        "merge_loop": {"ms": timing["merge_loop_ms"], "iterations": timing["iterations"], "merges": timing["merges"],
+                       "us_per_merge": timing["merge_loop_ms"] * 1e3 / max(1, timing["merges"]), "pair_init_ms": timing["pair_init_ms"]},
+        "encode": {"metric": "encode_GBps_corpus_to_uint16", "value": total / enc_ms / 1e6, "unit": "GB/s",
+                   "e2e": {"value": total / enc_e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(n_enc), "d2h_bytes_per_step": int(2 * n_ids_local),
+                           "api": "BPETokenizer.encode_file_to_array(path) (= encode_iterable(open(path)) as an array)"},
+                   "ids": n_ids_total, "algorithmic_bytes": int(total + 2 * n_ids_total), "roundtrip_decode_equals_input": roundtrip_ok},
+        "distinct_pretokens": int(n_unique), "pretokens": int(n_tokens), "merges": len(merges),
+        "kernels": kernels, "clocks": clocks,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        t0 = time.perf_counter()
+        line["cpu_baseline"] = cpu_train_sample(path, total, min(total, args.cpu_sample_bytes))
+        line["encode"]["cpu_baseline"] = cpu_encode_sample(path, vocab, merges, min(total, args.cpu_sample_bytes // 8))
+        log(f"[bench] cpu baseline: train {line['cpu_baseline']['value']:.1f} s, encode {line['encode']['cpu_baseline']['value'] * 1e3:.2f} MB/s "
+            f"({time.perf_counter() - t0:.1f} s)")
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--bytes", type=int, default=int(os.environ.get("BPE_BENCH_BYTES", 2_100_000_000)))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-sample-bytes", type=int, default=64_000_000)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    try:
+        run_gpu(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -272,15 +272,16 @@ class Engine:
                                         n + 1, C.byref(n_out), self._stream()))
         return out[:n_out.value]
 
-    def decode(self, d_ids, vocab_blob: np.ndarray, vocab_off: np.ndarray, max_token_len: int):
+    def decode(self, d_ids, vocab_blob: np.ndarray, vocab_off: np.ndarray):
+        """ids (device tensor, 2- or 4-byte elements) -> device tensor of the concatenated token bytes."""
         torch = self.torch
         n_ids = int(d_ids.numel())
         elem = d_ids.element_size()
-        cap = n_ids * max(3, max_token_len) + 16
-        out = torch.empty(cap, dtype=torch.uint8, device=f"cuda:{self.device}")
         n_bytes = C.c_uint64(0)
-        self._check(self.lib.bpe_decode(self.ctx, d_ids.data_ptr(), elem, n_ids, _np_ptr(vocab_blob), _np_ptr(vocab_off),
-                                        len(vocab_off) - 1, out.data_ptr(), cap, C.byref(n_bytes), self._stream()))
+        args = [self.ctx, d_ids.data_ptr(), elem, n_ids, _np_ptr(vocab_blob), _np_ptr(vocab_off), len(vocab_off) - 1]
+        self._check(self.lib.bpe_decode(*args, None, 0, C.byref(n_bytes), self._stream()))  # size query
+        out = torch.empty(n_bytes.value + 16, dtype=torch.uint8, device=f"cuda:{self.device}")
+        self._check(self.lib.bpe_decode(*args, out.data_ptr(), n_bytes.value, C.byref(n_bytes), self._stream()))
         return out[:n_bytes.value]
 
 

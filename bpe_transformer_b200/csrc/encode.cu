@@ -385,6 +385,7 @@ int run_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_id
     CUDA_TRY(ctx, cudaMemcpyAsync(&total, tile_off + n_tiles, 8, cudaMemcpyDeviceToHost, s));
     CUDA_TRY(ctx, cudaStreamSynchronize(s));
     *n_bytes = total;
+    if (!d_bytes) return BPE_OK;  // size query
     if (total > cap) return ctx_fail(ctx, BPE_ERR_CAPACITY, "output buffer too small");
     {
         KernelTimer t(ctx, "decode_write_kernel", s);

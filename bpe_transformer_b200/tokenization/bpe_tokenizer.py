@@ -134,8 +134,9 @@ class BPETokenizer(Tokenizer):
         get = self._vocab.get
         return b"".join(get(i, replacement) for i in ids).decode(ENCODING_STD, errors="replace")
 
-    def decode_array(self, ids, engine: "_lib.Engine | None" = None) -> bytes:
-        """GPU decode of a device / numpy id array to the concatenated bytes (no UTF-8 repair)."""
+    def decode_array(self, ids, engine: "_lib.Engine | None" = None, to_host: bool = True):
+        """GPU decode of a device / numpy id array to the concatenated bytes (no UTF-8 repair): `bytes`, or the
+        uint8 device tensor with to_host=False."""
         import torch
 
         engine = engine or _lib.get_engine()
@@ -149,8 +150,8 @@ class BPETokenizer(Tokenizer):
             lens[k + 1] = len(v)
         off = np.cumsum(lens, dtype=np.uint64)
         blob = np.frombuffer(b"".join(self._vocab.get(k, b"") for k in range(n_vocab)) + b"\0", dtype=np.uint8).copy()
-        out = engine.decode(ids, blob, off, int(lens.max()) if n_vocab else 3)
-        return out.cpu().numpy().tobytes()
+        out = engine.decode(ids, blob, off)
+        return out.cpu().numpy().tobytes() if to_host else out
 
     def encode_iterable(self, iterable: Iterable[str], n_workers: int | None = None) -> Iterator[int]:
         """Lazily encode an iterable of strings (:339-423).  Text is buffered, cut after the LAST newline of the

@@ -135,7 +135,8 @@ int bpe_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint64_t* 
 
 /* BPETokenizer.decode's byte concatenation (bpe_tokenizer.py:119-137): writes vocab[id] for every id
  * (U+FFFD bytes EF BF BD for ids without an entry) to d_bytes; the vocabulary comes as h_vocab_blob /
- * h_vocab_off over ids 0..n_vocab-1 (empty entry = no such id).  *n_bytes = bytes produced. */
+ * h_vocab_off over ids 0..n_vocab-1 (empty entry = no such id).  *n_bytes = bytes produced; with d_bytes == NULL
+ * only the size is computed. */
 int bpe_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_ids, const uint8_t* h_vocab_blob,
                const uint64_t* h_vocab_off, uint32_t n_vocab, uint8_t* d_bytes, uint64_t cap, uint64_t* n_bytes,
                void* stream);
