@@ -25,6 +25,7 @@ SYMBOLS = [
     "bpe_ctx_create", "bpe_ctx_destroy", "bpe_last_error", "bpe_ctx_configure", "bpe_set_special_tokens", "bpe_scan",
     "bpe_count", "bpe_unique_stats", "bpe_unique_export", "bpe_unique_import", "bpe_unique_reset", "bpe_train",
     "bpe_train_timing", "bpe_load_model", "bpe_encode", "bpe_decode", "bpe_kernel_times", "bpe_set_profiling",
+    "bpe_decode_noalloc",
 ]
 
 
@@ -76,6 +77,8 @@ def load_library():
         lib.bpe_encode.argtypes = [vp, u8p, C.c_uint64, u64p, C.c_uint64, C.c_uint32, u32p, vp, C.c_int, C.c_uint64,
                                    C.POINTER(C.c_uint64), vp]
         lib.bpe_decode.argtypes = [vp, vp, C.c_int, C.c_uint64, u8p, u64p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_uint64), vp]
+        lib.bpe_decode_noalloc.argtypes = [vp, C.c_int, C.c_uint64, u8p, u64p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_uint64), vp,
+                                           C.c_char_p, C.c_size_t]
         lib.bpe_kernel_times.argtypes = [vp, C.POINTER(KernelTime), C.c_int]
         lib.bpe_set_profiling.argtypes = [vp, C.c_int]
         for name in SYMBOLS:

@@ -396,3 +396,102 @@ int run_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_id
     CUDA_TRY(ctx, cudaStreamSynchronize(s));
     return BPE_OK;
 }
+
+// ================================================================================================================
+// bpe_decode_noalloc — ids -> bytes for callers that must not allocate device memory (include/bpe_b200.h).
+//
+// Same kernels as run_decode() above.  What differs is where the working memory comes from: the vocabulary is
+// the caller's own device buffer, and the per-tile byte counts and offsets (the only scratch the three kernels
+// need) live in a fixed array that is part of the library image.  The library reserves it on every GPU that
+// loads it, for the life of the process: 768 KiB per GPU, enough for BPE_NOALLOC_MAX_IDS ids per call.
+// ================================================================================================================
+#include <cstdio>
+#include <mutex>
+
+#define NOALLOC_MAX_TILES ((uint64_t)BPE_NOALLOC_MAX_IDS / ENC_THREADS)
+#define NOALLOC_OFF_BYTES ((NOALLOC_MAX_TILES + 1) * 8)                       /* uint64 tile offsets, one extra for the total */
+#define NOALLOC_SCRATCH_BYTES ((NOALLOC_OFF_BYTES + NOALLOC_MAX_TILES * 4 + 255) / 256 * 256)
+
+// In host code this name is only a handle for cudaGetSymbolAddress(); it is not a device address.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+#define NOALLOC_MAX_DEVICES 64
+static void* g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of g_noalloc_scratch, per GPU; null until set up
+static std::mutex g_noalloc_mutex;
+
+static void noalloc_message(char* h_err, size_t h_err_cap, const char* what, cudaError_t e = cudaSuccess) {
+    if (!h_err || !h_err_cap) return;
+    if (e != cudaSuccess) snprintf(h_err, h_err_cap, "%s: %s", what, cudaGetErrorString(e));
+    else snprintf(h_err, h_err_cap, "%s", what);
+}
+
+// Once per GPU, with that GPU current: ask the runtime where this GPU's copy of the array lives.
+static cudaError_t noalloc_setup(int device, void** out) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+
+extern "C" int bpe_decode_noalloc(const void* d_ids, int id_elem_bytes, uint64_t n_ids, const uint8_t* d_vocab_blob,
+                                  const uint64_t* d_vocab_off, uint32_t n_vocab, uint8_t* d_bytes, uint64_t cap,
+                                  uint64_t* n_bytes, void* stream, char* h_err, size_t h_err_cap) {
+    if (h_err && h_err_cap) h_err[0] = 0;
+    if (!n_bytes || (id_elem_bytes != 2 && id_elem_bytes != 4) || (n_ids && (!d_ids || !d_vocab_off))) {
+        noalloc_message(h_err, h_err_cap, "bpe_decode_noalloc: bad arguments (ids must be 2 or 4 bytes wide, pointers non-null)");
+        return BPE_ERR_ARGUMENT;
+    }
+    *n_bytes = 0;
+    if (n_ids > (uint64_t)BPE_NOALLOC_MAX_IDS) {
+        if (h_err && h_err_cap)
+            snprintf(h_err, h_err_cap, "bpe_decode_noalloc: %llu ids in one call, the built-in scratch holds at most %llu; split the call or use bpe_decode",
+                     (unsigned long long)n_ids, (unsigned long long)BPE_NOALLOC_MAX_IDS);
+        return BPE_ERR_CAPACITY;
+    }
+    if (n_ids == 0) return BPE_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess || device < 0 || device >= NOALLOC_MAX_DEVICES) {
+        noalloc_message(h_err, h_err_cap, "bpe_decode_noalloc: cudaGetDevice", e);
+        return BPE_ERR_CUDA;
+    }
+    void* base = nullptr;
+    if ((e = noalloc_setup(device, &base)) != cudaSuccess) {
+        noalloc_message(h_err, h_err_cap, "bpe_decode_noalloc: cudaGetSymbolAddress", e);
+        return BPE_ERR_CUDA;
+    }
+    // Every word the kernels read below is written earlier in this same call (tile_total by decode_len_kernel,
+    // tile_off by scan_totals_kernel), so what the previous call left behind is never seen: nothing needs clearing.
+    uint64_t* tile_off = reinterpret_cast<uint64_t*>(base);
+    uint32_t* tile_total = reinterpret_cast<uint32_t*>(static_cast<unsigned char*>(base) + NOALLOC_OFF_BYTES);
+    const uint64_t n_tiles = (n_ids + ENC_THREADS - 1) / ENC_THREADS;
+    if (id_elem_bytes == 2) decode_len_kernel<uint16_t><<<(unsigned)n_tiles, ENC_THREADS, 0, s>>>((const uint16_t*)d_ids, n_ids, d_vocab_off, n_vocab, tile_total);
+    else decode_len_kernel<uint32_t><<<(unsigned)n_tiles, ENC_THREADS, 0, s>>>((const uint32_t*)d_ids, n_ids, d_vocab_off, n_vocab, tile_total);
+    scan_totals_kernel<<<1, 1024, 0, s>>>(tile_total, n_tiles, tile_off);
+    if ((e = cudaGetLastError()) != cudaSuccess) { noalloc_message(h_err, h_err_cap, "bpe_decode_noalloc: kernel launch", e); return BPE_ERR_CUDA; }
+    uint64_t total = 0;
+    if ((e = cudaMemcpyAsync(&total, tile_off + n_tiles, 8, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+        (e = cudaStreamSynchronize(s)) != cudaSuccess) {
+        noalloc_message(h_err, h_err_cap, "bpe_decode_noalloc: reading the size", e);
+        return BPE_ERR_CUDA;
+    }
+    *n_bytes = total;
+    if (!d_bytes) return BPE_OK;  // size query
+    if (total > cap) {
+        noalloc_message(h_err, h_err_cap, "bpe_decode_noalloc: output buffer too small (*n_bytes holds the size needed)");
+        return BPE_ERR_CAPACITY;
+    }
+    if (id_elem_bytes == 2) decode_write_kernel<uint16_t><<<(unsigned)n_tiles, ENC_THREADS, 0, s>>>((const uint16_t*)d_ids, n_ids, d_vocab_blob, d_vocab_off, n_vocab, tile_off, d_bytes);
+    else decode_write_kernel<uint32_t><<<(unsigned)n_tiles, ENC_THREADS, 0, s>>>((const uint32_t*)d_ids, n_ids, d_vocab_blob, d_vocab_off, n_vocab, tile_off, d_bytes);
+    if ((e = cudaGetLastError()) != cudaSuccess || (e = cudaStreamSynchronize(s)) != cudaSuccess) {
+        noalloc_message(h_err, h_err_cap, "bpe_decode_noalloc: writing the bytes", e);
+        return BPE_ERR_CUDA;
+    }
+    return BPE_OK;
+}

@@ -141,6 +141,27 @@ int bpe_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_id
                const uint64_t* h_vocab_off, uint32_t n_vocab, uint8_t* d_bytes, uint64_t cap, uint64_t* n_bytes,
                void* stream);
 
+/* (No counterpart in the reference.)  bpe_decode for callers that cannot allocate device memory: a worker that
+ * turns id batches back into text next to a training or serving process which has already handed all of the
+ * GPU's memory to its own allocator (a raw cudaMalloc then fails or fragments that arena), or a latency-critical
+ * loop that cannot afford the device-wide synchronisation a cudaMalloc / cudaFree implies.  It needs no context
+ * and calls no cudaMalloc, cudaFree or any other allocating routine: inputs and outputs are the caller's
+ * (the vocabulary too — d_vocab_blob / d_vocab_off are DEVICE pointers here, laid out as in bpe_decode), and the
+ * per-tile sizes and offsets go into a fixed 768 KiB array inside the library image, which every GPU that loads
+ * the library holds until the process exits.  Hence the limit: at most BPE_NOALLOC_MAX_IDS ids per call; more
+ * returns BPE_ERR_CAPACITY with a message, and the caller splits the batch.
+ *   - Works on the calling thread's current device.  The first call on a device looks the array's device address
+ *     up (cudaGetSymbolAddress); make that first call before any stream capture begins on that device.
+ *   - All calls on a GPU share the one array, which still holds whatever the previous call wrote.  Nothing in it has
+ *     to start at zero (every word is written before it is read within a call), but two calls that overlap on the
+ *     GPU — different streams or host threads — race on it: serialise them.
+ *   - d_bytes == NULL only computes *n_bytes.  h_err (may be NULL) receives a message of at most h_err_cap bytes on
+ *     failure.  Returns after the work on `stream` has completed. */
+#define BPE_NOALLOC_MAX_IDS (1u << 24)
+int bpe_decode_noalloc(const void* d_ids, int id_elem_bytes, uint64_t n_ids, const uint8_t* d_vocab_blob,
+                       const uint64_t* d_vocab_off, uint32_t n_vocab, uint8_t* d_bytes, uint64_t cap,
+                       uint64_t* n_bytes, void* stream, char* h_err, size_t h_err_cap);
+
 /* Kernels launched on this context since the last bpe_set_profiling(): fills up to `max` entries of
  * (name, milliseconds, launches); returns the number of entries.  Launches are always counted; milliseconds
  * (CUDA events on the launching stream) only while profiling is on. */
