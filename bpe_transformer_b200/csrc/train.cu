@@ -1,15 +1,24 @@
 // train.cu — the greedy merge loop of BPETrainer (bpe_transformer/tokenization/bpe_trainer.py:169-426).
 //
-// State, all in HBM / L2 (a 2 GB TinyStories-shaped corpus has ~10^5 distinct pretokens, ~10^6 symbols):
-//   words     distinct pretokens as arrays of token ids (sym[off .. off+len)), their counts
-//   pairs     open-addressing table (a, b) -> signed 64-bit count, plus a list of occupied slots
-//   tokens    byte strings, a lexicographic rank per token (ties in count are broken on bytes, :36-67)
-//   postings  for every learned token X the words that were rewritten when X was created.  A pair that
-//             contains X can only occur in those words, so a merge step visits wl[X] instead of all words
-//             (the reference's pair -> pretokens inverted index, :186-199, :291-301, keyed by token;
-//             entries go stale and are re-checked on visit like :260-262).
-// One persistent cooperative kernel runs the whole loop; a step is: argmax over live pairs -> grid sync ->
-// rewrite the posting list's words + count deltas + rank maintenance -> grid sync.  No host round trip.
+// State, all in HBM / L2 (a 2 GB TinyStories-shaped corpus has ~2*10^5 distinct pretokens, ~2*10^6 symbols):
+//   words     distinct pretokens as arrays of token ids (sym[off .. off+len), 16-byte aligned), their counts
+//   pairs     open-addressing table (a, b) -> signed 64-bit count, a list of occupied slots, and a HOT list: the
+//             pairs whose count is at least a threshold T — the argmax looks only at those
+//   tokens    byte strings plus an 8-byte big-endian prefix key (ties in count are broken on bytes, :36-67)
+//   postings  for every learned token X the words that were rewritten when X was created.  A pair that contains
+//             X can only occur in those words, so a merge step visits wl[X] instead of all words (the reference's
+//             pair -> pretokens inverted index, :186-199, :291-301, keyed by token; entries go stale and are
+//             re-checked on visit like :260-262).
+//
+// The loop is strictly sequential (~10^4 dependent steps) and each step touches little data, so it is LATENCY bound.
+// One persistent kernel runs it, launched as ONE thread-block cluster (16 CTAs):
+//   * CTA 0 drives.  A "light" step (posting list of <= 2048 words: ~85 % of the steps) is done by CTA 0 alone and
+//     synchronises with __syncthreads only: argmax over the hot list -> filter the posting list (one thread per
+//     word, 16-byte loads) -> rewrite the matching words (one WARP per word) -> bookkeeping.
+//   * A "heavy" step (a pair of bytes, whose candidates are ALL words, or a long posting list) is broadcast to the
+//     other CTAs, which sleep on the hardware cluster barrier in between.
+// For word tables beyond ~4*10^6 words the same code runs as a cooperative grid (grid barrier instead of the
+// cluster barrier).  No host round trip inside the loop.
 //
 // The count deltas reproduce the reference exactly, including its double counting:
 // removed neighbours are read from the ORIGINAL word (:414-417), added neighbours are counted once per new
@@ -18,79 +27,171 @@
 #include <cooperative_groups.h>
 
 #include <algorithm>
+#include <climits>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 
 namespace cg = cooperative_groups;
 
-#define TRAIN_THREADS 512
 #define PAIR_PROBE_LIMIT 8192
+#define RETIRED (-(1ll << 62))  // count of a pair that was merged (or found to have no occurrence): never positive again
+#define LIGHT_MAX 2048u         // posting lists up to this length are handled by the driver CTA alone
+#define QUEUE_CAP 2048u
+#define NONE 0xFFFFFFFFu
 
 namespace {
 
 struct Best {
     long long cnt;  // 0 = none
-    uint32_t ra, rb;
     unsigned long long key;
     uint32_t slot;
 };
 
-__device__ __forceinline__ bool better(const Best& x, const Best& y) {
-    if (x.cnt != y.cnt) return x.cnt > y.cnt;
-    if (x.ra != y.ra) return x.ra > y.ra;
-    if (x.rb != y.rb) return x.rb > y.rb;
-    return x.key > y.key;  // equal (count, bytes, bytes) on different id pairs: unpinned in the reference
-}
+struct Command {  // driver CTA -> helper CTAs, through global memory, ordered by the cluster / grid barrier
+    uint32_t op;  // 0 = exit, 1 = rewrite
+    uint32_t a, b, x, list_tok, list_len;
+    long long threshold;
+};
 
 struct Ctrl {
     unsigned int n_live;      // occupied pair slots (length of `live`)
     unsigned int wl_cursor;   // posting pool cursor
     unsigned int n_words;
     unsigned int sym_cursor;
-    unsigned int rmax[2];     // 1 + highest rank among tokens that sort below the new token
-    unsigned int req[2];      // 1 + rank of a token with the same bytes as the new token
     unsigned int n_merges;
     unsigned int n_iters;
-    unsigned int blob_cursor;
+    unsigned int n_hot;       // length of `hot`
+    unsigned int n_rebuilds;
+    unsigned int n_heavy;
     unsigned int pad;
+    Command cmd;
+    unsigned long long phase_clk[8];  // developer trace: SM cycles of the driver's thread 0 per phase, summed over iterations
 };
 
 struct TrainState {
     // words
     uint32_t* w_off; uint32_t* w_len; long long* w_cnt; uint32_t* sym;
     // pairs
-    unsigned long long* ph_key; long long* ph_cnt; uint8_t* ph_dead; uint32_t* live; uint64_t ph_mask;
+    unsigned long long* ph_key; long long* ph_cnt; uint32_t* live; ulonglong2* hot; uint64_t ph_mask;
     // tokens
-    uint32_t* tk_off; uint8_t* tk_blob; uint32_t blob_cap; uint32_t* rank; uint32_t* wl_off; uint32_t* wl_len;
+    uint32_t* tk_off; uint8_t* tk_blob; uint32_t blob_cap; unsigned long long* tk_pre; uint32_t* wl_off; uint32_t* wl_len;
     uint32_t* wl_pool; uint32_t wl_cap;
     uint32_t* m_a; uint32_t* m_b;
-    Best* block_best;
     Ctrl* ctrl;
+    uint32_t* trace;  // optional (BPE_B200_TRAIN_TRACE): per iteration {ns, list length, 1 = all words, matched}
     uint32_t* status;
     uint32_t first_new_id, vocab_size;
+    uint32_t flags;  // bit 0: never use the shared-memory cache (experiments)
 };
 
-__device__ __forceinline__ void pair_add(const TrainState& S, uint32_t a, uint32_t b, long long delta) {
-    unsigned long long key = (((unsigned long long)a << 32) | b) + 1ull;
+// Slot of pair `key` in the global table, inserted on first sight (compare-and-swap first: one round trip for a new pair).
+__device__ __forceinline__ uint64_t pair_slot(const TrainState& S, unsigned long long key) {
     uint64_t slot = (key * 0x9E3779B97F4A7C15ull >> 20) & S.ph_mask;
     for (int probe = 0; probe < PAIR_PROBE_LIMIT; probe++) {
-        unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(S.ph_key + slot);
+        unsigned long long cur = atomicCAS(S.ph_key + slot, 0ull, key);
         if (cur == 0) {
-            cur = atomicCAS(S.ph_key + slot, 0ull, key);
-            if (cur == 0) {
-                unsigned int idx = atomicAdd(&S.ctrl->n_live, 1u);
-                S.live[idx] = (uint32_t)slot;  // n_live <= number of slots
-                cur = key;
-            }
+            unsigned int idx = atomicAdd(&S.ctrl->n_live, 1u);
+            S.live[idx] = (uint32_t)slot;  // n_live <= number of slots
+            return slot;
         }
-        if (cur == key) {
-            atomicAdd(reinterpret_cast<unsigned long long*>(S.ph_cnt + slot), (unsigned long long)delta);
-            return;
-        }
+        if (cur == key) return slot;
         slot = (slot + 1) & S.ph_mask;
     }
     set_status(S.status, ST_PAIR_TABLE_FULL);
+    return 0;
 }
+
+// Count updates straight to the global table.  A pair whose count rises to or above the threshold is appended to the
+// global "pending hot" list, which the driver drains (duplicates are harmless there).
+struct GlobalAdder {
+    const TrainState& S;
+    long long threshold;
+    __device__ __forceinline__ void operator()(uint32_t a, uint32_t b, long long delta) const {
+        unsigned long long key = (((unsigned long long)a << 32) | b) + 1ull;
+        uint64_t slot = pair_slot(S, key);
+        if (delta < 0) {  // cannot enter the hot list: no need to wait for the old value
+            atomicAdd(reinterpret_cast<unsigned long long*>(S.ph_cnt + slot), (unsigned long long)delta);
+            return;
+        }
+        long long before = (long long)atomicAdd(reinterpret_cast<unsigned long long*>(S.ph_cnt + slot), (unsigned long long)delta);
+        if (before < threshold && before + delta >= threshold) {
+            unsigned int h = atomicAdd(&S.ctrl->n_hot, 1u);
+            if (h <= S.ph_mask) S.hot[h] = make_ulonglong2(key, slot);
+        }
+    }
+};
+
+// ---- the driver CTA's shared-memory cache of the hot pairs -------------------------------------------------------------
+// key / global slot / a COPY of the count for every pair with count >= T (plus leftovers), and a small hash index over
+// the keys.  The global table stays exact (every update goes there too, fire-and-forget); the copy lets the argmax of a
+// light step run without touching global memory.  Entries appended during a step get their count from global memory
+// when the step closes; after a heavy step (other CTAs updated counts) all copies are reloaded.
+#define HC 6144u      // cache entries
+#define CACHE_FILL 3072u  // entries a rebuild aims for (the rest is room for pairs that rise past T)
+#define SUB_BINS 1024u
+#define HIDX 16384u   // index slots (power of two)
+struct HotCache {
+    unsigned long long key[HC];  // 0 = hole (duplicate that lost the race)
+    long long cnt[HC];
+    uint32_t slot[HC];
+    unsigned short index[HIDX];  // entry + 1, 0 = empty
+    unsigned int n;              // entries in use (may exceed HC: overflow, forces a rebuild)
+};
+
+__device__ __forceinline__ uint32_t hc_hash(unsigned long long key) { return (uint32_t)((key * 0xD6E8FEB86659FD93ull) >> 50); }
+
+__device__ __forceinline__ int hc_find(const HotCache& H, unsigned long long key) {
+    uint32_t h = hc_hash(key) & (HIDX - 1);
+    for (;;) {
+        unsigned int v = *reinterpret_cast<const volatile unsigned short*>(&H.index[h]);
+        if (v == 0) return -1;
+        if (H.key[v - 1] == key) return (int)v - 1;
+        h = (h + 1) & (HIDX - 1);
+    }
+}
+
+// Appends (key, slot) with count `cnt`; a concurrent duplicate loses and becomes a hole.
+__device__ __forceinline__ void hc_append(HotCache& H, unsigned long long key, uint32_t slot, long long cnt) {
+    unsigned int idx = atomicAdd(&H.n, 1u);
+    if (idx >= HC) return;
+    H.key[idx] = key; H.slot[idx] = slot; H.cnt[idx] = cnt;
+    __threadfence_block();
+    uint32_t h = hc_hash(key) & (HIDX - 1);
+    for (;;) {
+        unsigned short v = *reinterpret_cast<volatile unsigned short*>(&H.index[h]);
+        if (v == 0) {
+            v = atomicCAS(&H.index[h], (unsigned short)0, (unsigned short)(idx + 1));
+            if (v == 0) return;
+        }
+        if (H.key[v - 1] == key) { H.key[idx] = 0; return; }
+        h = (h + 1) & (HIDX - 1);
+    }
+}
+
+struct CacheAdder {
+    const TrainState& S;
+    HotCache& H;
+    long long threshold;
+    __device__ __forceinline__ void operator()(uint32_t a, uint32_t b, long long delta) const {
+        unsigned long long key = (((unsigned long long)a << 32) | b) + 1ull;
+        int e = hc_find(H, key);
+        if (e >= 0) {  // hot already: update the copy, post the update to the global table without waiting
+            atomicAdd(reinterpret_cast<unsigned long long*>(&H.cnt[e]), (unsigned long long)delta);
+            atomicAdd(reinterpret_cast<unsigned long long*>(S.ph_cnt + H.slot[e]), (unsigned long long)delta);
+            return;
+        }
+        uint64_t slot = pair_slot(S, key);
+        if (delta < 0) {
+            atomicAdd(reinterpret_cast<unsigned long long*>(S.ph_cnt + slot), (unsigned long long)delta);
+            return;
+        }
+        long long before = (long long)atomicAdd(reinterpret_cast<unsigned long long*>(S.ph_cnt + slot), (unsigned long long)delta);
+        if (before < threshold && before + delta >= threshold) hc_append(H, key, (uint32_t)slot, 0);  // count: loaded when the step closes
+    }
+};
 
 // ---- build the word table from the table of distinct pretokens (bpe_trainer.py:188-190: len 1 is skipped) ----
 __global__ void words_build_kernel(UniqueTable ut, TrainState S) {
@@ -99,7 +200,7 @@ __global__ void words_build_kernel(UniqueTable ut, TrainState S) {
     uint32_t len = ut.len[slot];
     if (len < 2) return;
     unsigned int w = atomicAdd(&S.ctrl->n_words, 1u);
-    unsigned int off = atomicAdd(&S.ctrl->sym_cursor, len);
+    unsigned int off = atomicAdd(&S.ctrl->sym_cursor, (len + 3u) & ~3u);  // 16-byte aligned: scanned with uint4 loads
     S.w_off[w] = off; S.w_len[w] = len; S.w_cnt[w] = (long long)ut.cnt[slot];
     const uint8_t* src = ut.pool + ut.pool_off[slot];
     for (uint32_t k = 0; k < len; k++) S.sym[off + k] = src[k];
@@ -115,38 +216,78 @@ __global__ void pairs_init_kernel(TrainState S, uint32_t n_words) {
     uint32_t prev = s[0];
     for (uint32_t k = 1; k < len; k++) {
         uint32_t cur = s[k];
-        pair_add(S, prev, cur, c);
+        GlobalAdder{S, LLONG_MAX}(prev, cur, c);  // hot pairs are collected by the merge loop's first rebuild
         prev = cur;
     }
 }
 
-// Lexicographic comparison of token t's bytes with the concatenation bytes(a) + bytes(b).
-__device__ int cmp_with_concat(const TrainState& S, uint32_t t, const uint8_t* A, uint32_t la, const uint8_t* B, uint32_t lb) {
-    uint32_t o = __ldcg(S.tk_off + t), lt = __ldcg(S.tk_off + t + 1) - o;
-    const uint8_t* T = S.tk_blob + o;
-    uint32_t lx = la + lb, n = lt < lx ? lt : lx;
+// ---- ordering of candidates: count, then (bytes(a), bytes(b)) as a tuple, then the id pair --------------------------
+// 8-byte big-endian zero-padded prefixes order two byte strings whenever they differ; equal prefixes fall back to the
+// bytes (a shorter string that is a prefix of a longer one pads with 0x00 <= any byte, so "prefixes differ" is decisive).
+__device__ int token_cmp(const TrainState& S, uint32_t t, uint32_t u) {
+    if (t == u) return 0;
+    unsigned long long pt = __ldcg(S.tk_pre + t), pu = __ldcg(S.tk_pre + u);
+    if (pt != pu) return pt < pu ? -1 : 1;
+    uint32_t ot = __ldcg(S.tk_off + t), lt = __ldcg(S.tk_off + t + 1) - ot, ou = __ldcg(S.tk_off + u), lu = __ldcg(S.tk_off + u + 1) - ou;
+    uint32_t n = lt < lu ? lt : lu;
     for (uint32_t i = 0; i < n; i++) {
-        uint32_t x = i < la ? A[i] : B[i - la];
-        uint32_t y = T[i];
-        if (y != x) return y < x ? -1 : 1;
+        uint32_t x = __ldcg(S.tk_blob + ot + i), y = __ldcg(S.tk_blob + ou + i);
+        if (x != y) return x < y ? -1 : 1;
     }
-    return (lt > lx) - (lt < lx);
+    return (lt > lu) - (lt < lu);
 }
 
-// One word: replace (a, b) by x left to right without overlap, apply the reference's count deltas.
-__device__ void rewrite_word(const TrainState& S, uint32_t w, uint32_t a, uint32_t b, uint32_t x) {
+__device__ __forceinline__ bool better(const TrainState& S, const Best& x, const Best& y) {
+    if (x.cnt != y.cnt) return x.cnt > y.cnt;
+    if (x.cnt <= 0 || x.key == y.key) return false;
+    int c = token_cmp(S, (uint32_t)((x.key - 1) >> 32), (uint32_t)((y.key - 1) >> 32));  // bpe_trainer.py:59-64
+    if (!c) c = token_cmp(S, (uint32_t)(x.key - 1), (uint32_t)(y.key - 1));
+    if (c) return c > 0;
+    return x.key > y.key;  // equal (count, bytes, bytes) on different id pairs: unpinned in the reference
+}
+
+__device__ __forceinline__ Best shfl_best(const Best& b, int o, bool down) {
+    Best r;
+    r.cnt = down ? __shfl_down_sync(0xFFFFFFFFu, b.cnt, o) : __shfl_xor_sync(0xFFFFFFFFu, b.cnt, o);
+    r.key = down ? __shfl_down_sync(0xFFFFFFFFu, b.key, o) : __shfl_xor_sync(0xFFFFFFFFu, b.key, o);
+    r.slot = down ? __shfl_down_sync(0xFFFFFFFFu, b.slot, o) : __shfl_xor_sync(0xFFFFFFFFu, b.slot, o);
+    return r;
+}
+
+// ---- word rewriting -----------------------------------------------------------------------------------------------------
+// Does the word contain (a, b)?  One thread, 16-byte loads (independent of one another, so they overlap).
+__device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, uint32_t a, uint32_t b) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(S.sym + S.w_off[w]);
+    uint4 v = __ldcg(s4);                        // every word owns at least 4 symbol slots: load before the length is known
+    const uint32_t len = __ldcg(S.w_len + w);
+    if (len < 2) return false;
+    bool hit = (v.x == a && v.y == b) | (2 < len && v.y == a && v.z == b) | (3 < len && v.z == a && v.w == b);
+    uint32_t prev = v.w;
+    for (uint32_t k = 4; k < len; k += 4) {
+        v = __ldcg(s4 + (k >> 2));
+        hit |= (prev == a && v.x == b) | (k + 1 < len && v.x == a && v.y == b) | (k + 2 < len && v.y == a && v.z == b) |
+               (k + 3 < len && v.z == a && v.w == b);
+        prev = v.w;
+    }
+    return hit;
+}
+
+// One word, one thread: replace (a, b) by x left to right without overlap, apply the reference's count deltas.
+// Returns whether anything matched.  (Words longer than a warp, and queue overflow.)
+template <class Adder>
+__device__ bool rewrite_word_serial(const TrainState& S, uint32_t w, uint32_t a, uint32_t b, uint32_t x, const Adder& add) {
     uint32_t* s = S.sym + S.w_off[w];
     uint32_t len = __ldcg(S.w_len + w);
-    if (len < 2) return;
+    if (len < 2) return false;
     long long c = S.w_cnt[w];
     uint32_t m = 0, j = 0, hits = 0;
     uint32_t cur = __ldcg(s), prev = 0;
     while (j < len) {
-        uint32_t nxt = (j + 1 < len) ? __ldcg(s + j + 1) : 0xFFFFFFFFu;
+        uint32_t nxt = (j + 1 < len) ? __ldcg(s + j + 1) : NONE;
         if (j + 1 < len && cur == a && nxt == b) {
-            if (j >= 1) pair_add(S, prev, cur, -c);                       // (s[j-1], s[j]) from the original word
-            uint32_t nn = (j + 2 < len) ? __ldcg(s + j + 2) : 0xFFFFFFFFu;
-            if (j + 2 < len) pair_add(S, nxt, nn, -c);                    // (s[j+1], s[j+2]) from the original word
+            if (j >= 1) add(prev, cur, -c);                               // (s[j-1], s[j]) from the original word
+            uint32_t nn = (j + 2 < len) ? __ldcg(s + j + 2) : NONE;
+            if (j + 2 < len) add(nxt, nn, -c);                            // (s[j+1], s[j+2]) from the original word
             s[m++] = x;
             hits++;
             prev = nxt; cur = nn; j += 2;
@@ -155,144 +296,370 @@ __device__ void rewrite_word(const TrainState& S, uint32_t w, uint32_t a, uint32
             prev = cur; cur = nxt; j += 1;
         }
     }
-    if (!hits) return;
+    if (!hits) return false;
     for (uint32_t k = 0; k < m; k++) {
         if (s[k] != x) continue;
-        if (k >= 1) pair_add(S, s[k - 1], x, c);
-        if (k + 1 < m) pair_add(S, x, s[k + 1], c);
+        if (k >= 1) add(s[k - 1], x, c);
+        if (k + 1 < m) add(x, s[k + 1], c);
     }
     S.w_len[w] = m;
-    unsigned int at = atomicAdd(&S.ctrl->wl_cursor, 1u);
-    if (at < S.wl_cap) S.wl_pool[at] = w; else set_status(S.status, ST_LIST_FULL);
+    return true;
 }
 
-__global__ void __launch_bounds__(TRAIN_THREADS) merge_loop_kernel(TrainState S) {
-    cg::grid_group grid = cg::this_grid();
-    __shared__ Best sh_best[TRAIN_THREADS / 32];
-    __shared__ Best sh_win;
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t gtid = blockIdx.x * blockDim.x + tid, gsize = gridDim.x * blockDim.x;
-    const bool leader = blockIdx.x == 0 && tid == 0;
-    const uint32_t n_words = S.ctrl->n_words;
-    const uint32_t NONE = 0xFFFFFFFFu;
+// One word per WARP (up to 32 symbols): every lane holds one symbol, the matches come from a ballot, the four count
+// deltas of a match are issued by two lanes at once, the new word is written back compacted.  Same deltas as the
+// serial version: for a match at j, removed (s[j-1], s[j]) and (s[j+1], s[j+2]) of the original word; added
+// (left neighbour in the new word, x) and (x, right neighbour in the new word), a neighbour being x itself when the
+// adjacent original positions were a match too.  Returns (warp-uniform) whether anything matched.
+template <class Adder>
+__device__ bool rewrite_word_warp(const TrainState& S, uint32_t w, uint32_t a, uint32_t b, uint32_t x, const Adder& add) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t len = __ldcg(S.w_len + w);
+    if (len < 2) return false;
+    if (len > 32) {
+        bool hit = lane == 0 ? rewrite_word_serial(S, w, a, b, x, add) : false;
+        return __shfl_sync(0xFFFFFFFFu, hit, 0);
+    }
+    uint32_t* s = S.sym + S.w_off[w];
+    const uint32_t me = lane < len ? __ldcg(s + lane) : NONE;
+    const long long c = S.w_cnt[w];
+    const uint32_t next1 = __shfl_down_sync(0xFFFFFFFFu, me, 1), prev1 = __shfl_up_sync(0xFFFFFFFFu, me, 1);
+    const bool cand = lane + 1 < len && me == a && next1 == b;
+    const uint32_t C = __ballot_sync(0xFFFFFFFFu, cand);
+    if (!C) return false;
+    bool match = cand;
+    if (a == b) {  // a run of candidates: left to right without overlap = every other one from the run's start
+        uint32_t starts = C & ~(C << 1);
+        uint32_t my_start = 31 - __clz(starts & (0xFFFFFFFFu >> (31 - lane)));
+        match = cand && !((lane - my_start) & 1u);
+    }
+    const uint32_t M = __ballot_sync(0xFFFFFFFFu, match);
+    const bool second = lane >= 1 && ((M >> (lane - 1)) & 1u);  // this lane holds the right half of a match
+    if (match && lane >= 1) {
+        add(prev1, me, -c);
+        add((lane >= 2 && ((M >> (lane - 2)) & 1u)) ? x : prev1, x, c);
+    }
+    if (second && lane + 1 < len) {
+        add(me, next1, -c);
+        add(x, ((M >> (lane + 1)) & 1u) ? x : next1, c);
+    }
+    __syncwarp();
+    if (lane < len && !second) s[lane - __popc(M & ((1u << lane) - 1u))] = match ? x : me;
+    if (lane == 0) S.w_len[w] = len - __popc(M);
+    return true;
+}
 
-    uint32_t next_id = S.first_new_id;
-    // Results of the previous step.  They reach memory at the start of the next step (leader thread), so
-    // phase 1 of that step reads them from these registers; from phase 2 on memory is current.
-    uint32_t prev_slot = NONE, prev_x = NONE, prev_rank = 0, prev_matched = 0;
-    uint32_t iter = 0;
+// The candidates of a heavy step, spread over all CTAs: every thread filters one candidate word per round, the CTA's
+// warps rewrite the hits.  Rewritten words are appended to the posting pool through the global cursor.
+template <int NT>
+__device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t n_words, uint32_t* sh_queue, unsigned int* sh_qn) {
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gsize = gridDim.x * NT;
+    const uint32_t* list = cmd.list_tok == NONE ? nullptr : S.wl_pool + __ldcg(S.wl_off + cmd.list_tok);
+    const uint32_t n_cand = list ? cmd.list_len : n_words;
+    const GlobalAdder add{S, cmd.threshold};
+    for (uint32_t base = blockIdx.x * NT; base < n_cand; base += gsize) {
+        if (tid == 0) *sh_qn = 0;
+        __syncthreads();
+        const uint32_t i = base + tid;
+        if (i < n_cand) {
+            const uint32_t w = list ? __ldcg(list + i) : i;
+            if (word_has_pair(S, w, cmd.a, cmd.b)) {
+                unsigned int q = atomicAdd(sh_qn, 1u);
+                if (q < QUEUE_CAP) sh_queue[q] = w;
+                else if (rewrite_word_serial(S, w, cmd.a, cmd.b, cmd.x, add)) {
+                    unsigned int at = atomicAdd(&S.ctrl->wl_cursor, 1u);
+                    if (at < S.wl_cap) S.wl_pool[at] = w; else set_status(S.status, ST_LIST_FULL);
+                }
+            }
+        }
+        __syncthreads();
+        const uint32_t qn = min(*sh_qn, QUEUE_CAP);
+        for (uint32_t k = warp; k < qn; k += NT / 32) {
+            const uint32_t w = sh_queue[k];
+            if (rewrite_word_warp(S, w, cmd.a, cmd.b, cmd.x, add) && lane == 0) {
+                unsigned int at = atomicAdd(&S.ctrl->wl_cursor, 1u);
+                if (at < S.wl_cap) S.wl_pool[at] = w; else set_status(S.status, ST_LIST_FULL);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+template <bool CLUSTER, int NT>
+__global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
+    auto sync_all = [] {
+        if constexpr (CLUSTER) cg::this_cluster().sync(); else cg::this_grid().sync();
+    };
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HotCache& H = *reinterpret_cast<HotCache*>(smem_raw);  // used by the driver CTA only
+    __shared__ Best sh_best[NT / 32];
+    __shared__ Best sh_win;
+    __shared__ uint32_t sh_queue[QUEUE_CAP];
+    __shared__ unsigned int sh_qn;
+    __shared__ unsigned int sh_hist[64];
+    __shared__ unsigned int sh_sub[SUB_BINS];
+    __shared__ long long sh_T;
+    __shared__ int sh_bit;
+    __shared__ unsigned int sh_above;
+    __shared__ Command sh_cmd;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t n_words = S.ctrl->n_words;
+
+    if (blockIdx.x != 0) {  // helper CTAs: asleep on the barrier until the driver broadcasts a heavy step
+        for (;;) {
+            sync_all();
+            if (tid == 0) {
+                const volatile Command* c = &S.ctrl->cmd;
+                sh_cmd.op = c->op; sh_cmd.a = c->a; sh_cmd.b = c->b; sh_cmd.x = c->x; sh_cmd.list_tok = c->list_tok;
+                sh_cmd.list_len = c->list_len; sh_cmd.threshold = c->threshold;
+            }
+            __syncthreads();
+            const Command cmd = sh_cmd;
+            if (cmd.op == 0) return;
+            heavy_rewrite<NT>(S, cmd, n_words, sh_queue, &sh_qn);
+            sync_all();
+        }
+    }
+
+    // ---- driver CTA -------------------------------------------------------------------------------------------------
+    const bool leader = tid == NT - 32;  // a warp of its own: its bookkeeping runs beside the other warps' work
+    const bool tracer = S.trace && tid == 0;
+    uint32_t next_id = S.first_new_id, iter = 0, wl_cur = 0, n_heavy = 0;
+    bool need_rebuild = true;
+    bool use_cache = !(S.flags & 1u);  // false: counts too flat for the cache (see the rebuild): argmax over the global table
+    long long T = LLONG_MAX, failed_T = 0;
+    uint32_t spins = 0;           // loop passes that did not finish a step (rebuilds): bounded, a bug must not hang the GPU
+    unsigned long long t_prev = 0;
+    if (S.trace && leader) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_prev));
 
     while (next_id < S.vocab_size) {
-        const uint32_t par = iter & 1;
-        // ---- phase 1: argmax over live pairs of (count, rank[a], rank[b]) --------------------------------------
-        if (leader) {
-            if (prev_slot != NONE) S.ph_dead[prev_slot] = 1;       // the winner never occurs again (bpe_trainer.py:243)
-            if (prev_x != NONE) { S.rank[prev_x] = prev_rank; S.wl_len[prev_x] = prev_matched; }
-            S.ctrl->rmax[par] = 0; S.ctrl->req[par] = 0;
+        // Cache invariant: every pair with count >= T has an entry (pairs are appended when their count rises past T;
+        // leftovers below T and holes are allowed).  If the best entry has count >= T it is the global argmax;
+        // otherwise T is lowered and the cache rebuilt from a log2 histogram of all counts.
+        if (need_rebuild && use_cache) {
+            if (++spins > 64) { if (tid == 0) set_status(S.status, ST_PAIR_TABLE_FULL); break; }
+            if (tid < 64) sh_hist[tid] = 0;
+            for (uint32_t k = tid; k < HIDX; k += NT) H.index[k] = 0;
+            if (tid == 0) H.n = 0;
+            __syncthreads();
+            const uint32_t n_all = __ldcg(&S.ctrl->n_live);
+            for (uint32_t i = tid; i < n_all; i += NT) {
+                long long cnt = __ldcg(S.ph_cnt + __ldcg(S.live + i));
+                if (cnt > 0) atomicAdd(&sh_hist[63 - __clzll(cnt)], 1u);
+            }
+            __syncthreads();
+            if (tid == 0) {  // the bin (power of two) in which the CACHE_FILL-th largest count lies
+                unsigned int above = sh_hist[63];
+                int bit = 63;
+                for (; bit > 0; bit--) {
+                    if (above + sh_hist[bit - 1] > CACHE_FILL) break;
+                    above += sh_hist[bit - 1];
+                }
+                sh_bit = bit;      // bins >= bit fit entirely (`above` pairs); bin bit - 1 does not (unless bit == 0)
+                sh_above = above;
+                sh_T = 1ll << bit;
+                S.ctrl->n_rebuilds++;
+            }
+            for (uint32_t k = tid; k < SUB_BINS; k += NT) sh_sub[k] = 0;
+            __syncthreads();
+            if (sh_bit > 0) {  // refine inside bin bit - 1 = [lo, 2 lo): SUB_BINS equal slices, take the upper ones that still fit
+                const long long lo = 1ll << (sh_bit - 1), width = lo >= SUB_BINS ? lo / SUB_BINS : 1;
+                for (uint32_t i = tid; i < n_all; i += NT) {
+                    long long cnt = __ldcg(S.ph_cnt + __ldcg(S.live + i));
+                    if (cnt >= lo && cnt < 2 * lo) atomicAdd(&sh_sub[(cnt - lo) / width], 1u);
+                }
+                __syncthreads();
+                if (tid == 0) {
+                    unsigned int above = sh_above;
+                    long long slice = (lo + width - 1) / width;  // slices in use
+                    while (slice > 0 && above + sh_sub[slice - 1] <= CACHE_FILL) above += sh_sub[--slice];
+                    sh_T = lo + slice * width;
+                }
+                __syncthreads();
+            }
+            T = sh_T;
+            // The previous threshold found nothing and the next lower one does not fit (many pairs with equal small
+            // counts): leave the cache and take the argmax over the whole table from here on.
+            if (T == failed_T) use_cache = false;
+            for (uint32_t i = tid; use_cache && i < n_all; i += NT) {
+                uint32_t slot = __ldcg(S.live + i);
+                long long cnt = __ldcg(S.ph_cnt + slot);
+                if (cnt >= T) hc_append(H, __ldcg(S.ph_key + slot), slot, cnt);
+            }
+            __syncthreads();
+            need_rebuild = false;
         }
-        const uint32_t n_live = __ldcg(&S.ctrl->n_live);
-        const uint32_t wl_start = __ldcg(&S.ctrl->wl_cursor);
-        Best best{0, 0, 0, 0, 0};
-        for (uint32_t i = gtid; i < n_live; i += gsize) {
-            uint32_t slot = __ldcg(S.live + i);
-            long long cnt = __ldcg(S.ph_cnt + slot);
-            if (cnt <= 0 || slot == prev_slot || __ldcg(S.ph_dead + slot)) continue;
-            unsigned long long key = __ldcg(S.ph_key + slot);
-            uint32_t a = (uint32_t)((key - 1) >> 32), b = (uint32_t)(key - 1);
-            Best c{cnt, a == prev_x ? prev_rank : __ldcg(S.rank + a), b == prev_x ? prev_rank : __ldcg(S.rank + b), key, slot};
-            if (better(c, best)) best = c;
+        if (!use_cache) T = LLONG_MAX;  // GlobalAdder never reports crossings
+
+        // ---- argmax over the cached pairs of (count, bytes(a), bytes(b)): shared memory only -------------------------------
+        long long c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0;
+        if (tracer) c0 = clock64();
+        const uint32_t n_cached = use_cache ? H.n : 0;
+        if (n_cached > HC) { need_rebuild = true; continue; }  // overflowed: compact (holes, leftovers) or raise T
+        Best best{0, 0, 0};
+        if (use_cache) {
+            for (uint32_t i = tid; i < n_cached; i += NT) {
+                Best c{H.cnt[i], H.key[i], i};
+                if (c.key && c.cnt > 0 && better(S, c, best)) best = c;
+            }
+        } else {
+            const uint32_t n_all = __ldcg(&S.ctrl->n_live);
+            for (uint32_t i = tid; i < n_all; i += NT) {
+                const uint32_t slot = __ldcg(S.live + i);
+                const long long cnt = __ldcg(S.ph_cnt + slot);
+                if (cnt <= 0 || cnt < best.cnt) continue;
+                Best c{cnt, __ldcg(S.ph_key + slot), slot};
+                if (better(S, c, best)) best = c;
+            }
         }
+        long long c0a = 0, c0b = 0, c0c = 0;
+        if (tracer) c0a = clock64();
         for (int o = 16; o; o >>= 1) {
-            Best other;
-            other.cnt = __shfl_down_sync(0xFFFFFFFFu, best.cnt, o);
-            other.ra = __shfl_down_sync(0xFFFFFFFFu, best.ra, o);
-            other.rb = __shfl_down_sync(0xFFFFFFFFu, best.rb, o);
-            other.key = __shfl_down_sync(0xFFFFFFFFu, best.key, o);
-            other.slot = __shfl_down_sync(0xFFFFFFFFu, best.slot, o);
-            if (better(other, best)) best = other;
+            Best other = shfl_best(best, o, true);
+            if (better(S, other, best)) best = other;
         }
+        if (tracer) c0b = clock64();
         if (lane == 0) sh_best[warp] = best;
         __syncthreads();
-        if (tid == 0) {
-            Best bb = sh_best[0];
-            for (uint32_t k = 1; k < TRAIN_THREADS / 32; k++) if (better(sh_best[k], bb)) bb = sh_best[k];
-            S.block_best[blockIdx.x] = bb;
-        }
-        grid.sync();
+        if (tracer) c0c = clock64();
         if (warp == 0) {
-            Best bb{0, 0, 0, 0, 0};
-            for (uint32_t k = lane; k < gridDim.x; k += 32) {
-                Best c;
-                c.cnt = __ldcg(&S.block_best[k].cnt); c.ra = __ldcg(&S.block_best[k].ra); c.rb = __ldcg(&S.block_best[k].rb);
-                c.key = __ldcg(&S.block_best[k].key); c.slot = __ldcg(&S.block_best[k].slot);
-                if (better(c, bb)) bb = c;
-            }
+            Best bb = lane < NT / 32 ? sh_best[lane] : Best{0, 0, 0};
             for (int o = 16; o; o >>= 1) {
-                Best other;
-                other.cnt = __shfl_xor_sync(0xFFFFFFFFu, bb.cnt, o);
-                other.ra = __shfl_xor_sync(0xFFFFFFFFu, bb.ra, o);
-                other.rb = __shfl_xor_sync(0xFFFFFFFFu, bb.rb, o);
-                other.key = __shfl_xor_sync(0xFFFFFFFFu, bb.key, o);
-                other.slot = __shfl_xor_sync(0xFFFFFFFFu, bb.slot, o);
-                if (better(other, bb)) bb = other;
+                Best other = shfl_best(bb, o, false);
+                if (better(S, other, bb)) bb = other;
             }
             if (lane == 0) sh_win = bb;
         }
         __syncthreads();
-        const Best win = sh_win;
-        if (win.cnt <= 0) break;  // nothing qualifies (bpe_trainer.py:242: heap exhausted)
+        if (tracer) c1 = clock64();
+        const Best win = sh_win;  // .slot = index of the cache entry (global slot without the cache)
+        if (!use_cache) {
+            if (win.cnt <= 0) break;  // nothing qualifies (bpe_trainer.py:242: heap exhausted)
+        } else if (win.cnt < T) {     // the best cached pair is below the threshold: pairs outside the cache may beat it
+            if (T <= 1) break;        // the cache held every pair with a positive count: nothing qualifies
+            failed_T = T;
+            need_rebuild = true;
+            continue;
+        }
+        spins = 0;
         const uint32_t a = (uint32_t)((win.key - 1) >> 32), b = (uint32_t)(win.key - 1), x = next_id;
 
-        // ---- phase 2: rewrite the words that can contain (a, b); keep the ranks ready for the new token ----------
-        const uint32_t oa = __ldcg(S.tk_off + a), ob = __ldcg(S.tk_off + b);
-        const uint32_t la_tok = __ldcg(S.tk_off + a + 1) - oa, lb_tok = __ldcg(S.tk_off + b + 1) - ob;
-        const uint8_t* A = S.tk_blob + oa;
-        const uint8_t* B = S.tk_blob + ob;
-        uint32_t list_tok = NONE, list_len = n_words;  // byte pairs: every word
+        // ---- the words that can contain (a, b): the shorter posting list of the two tokens, all words for two bytes ------
+        uint32_t list_tok = NONE, list_len = n_words;
         if (a >= S.first_new_id) { list_tok = a; list_len = __ldcg(S.wl_len + a); }
         if (b >= S.first_new_id) {
             uint32_t lb = __ldcg(S.wl_len + b);
             if (list_tok == NONE || lb < list_len) { list_tok = b; list_len = lb; }
         }
-        const uint32_t* list = (list_tok == NONE) ? nullptr : S.wl_pool + __ldcg(S.wl_off + list_tok);
-        for (uint32_t i = gtid; i < list_len; i += gsize) rewrite_word(S, list ? __ldcg(list + i) : i, a, b, x);
-
-        // Rank maintenance for x = bytes(a) + bytes(b): tokens that sort above it move up by one, its own rank
-        // becomes (highest rank below it) + 1, or the rank of a token with identical bytes.  Done speculatively:
-        // if the step merges nothing the order of the existing tokens is still intact.
-        unsigned int my_rmax = 0;
-        for (uint32_t t = gtid; t < x; t += gsize) {
-            int c = cmp_with_concat(S, t, A, la_tok, B, lb_tok);
-            uint32_t r = __ldcg(S.rank + t);
-            if (c > 0) S.rank[t] = r + 1;
-            else if (c < 0) my_rmax = max(my_rmax, r + 1);
-            else S.ctrl->req[par] = r + 1;
-        }
-        my_rmax = __reduce_max_sync(0xFFFFFFFFu, my_rmax);
-        if (lane == 0 && my_rmax) atomicMax(&S.ctrl->rmax[par], my_rmax);
-        if (leader) {  // speculative too: overwritten by the next attempt if this step merges nothing
-            uint32_t o = __ldcg(S.tk_off + x);
-            if (o + la_tok + lb_tok <= S.blob_cap) {
-                for (uint32_t i = 0; i < la_tok; i++) S.tk_blob[o + i] = A[i];
-                for (uint32_t i = 0; i < lb_tok; i++) S.tk_blob[o + la_tok + i] = B[i];
+        const uint32_t wl_start = wl_cur;
+        const uint32_t first_new_entry = n_cached;
+        uint32_t matched = 0;
+        if (tid == 0) sh_qn = 0;
+        if (leader) {  // bookkeeping for x beside the rewrite (speculative: overwritten if the step merges nothing)
+            const uint32_t oa = __ldcg(S.tk_off + a), ob = __ldcg(S.tk_off + b), o = __ldcg(S.tk_off + x);
+            const uint32_t la = __ldcg(S.tk_off + a + 1) - oa, lb = __ldcg(S.tk_off + b + 1) - ob;
+            unsigned long long px = 0;
+            if (o + la + lb <= S.blob_cap) {
+                for (uint32_t i = 0; i < la + lb; i++) {
+                    uint8_t v = i < la ? S.tk_blob[oa + i] : S.tk_blob[ob + i - la];
+                    S.tk_blob[o + i] = v;
+                    if (i < 8) px |= (unsigned long long)v << (56 - 8 * i);
+                }
             } else set_status(S.status, ST_LIST_FULL);
-            S.tk_off[x + 1] = o + la_tok + lb_tok;
+            S.tk_off[x + 1] = o + la + lb;
+            S.tk_pre[x] = px;
             S.m_a[x - S.first_new_id] = a; S.m_b[x - S.first_new_id] = b;
             S.wl_off[x] = wl_start;
         }
-        grid.sync();
-        const uint32_t matched = __ldcg(&S.ctrl->wl_cursor) - wl_start;
-        const uint32_t req = __ldcg(&S.ctrl->req[par]), rmax = __ldcg(&S.ctrl->rmax[par]);
-        prev_slot = win.slot;
+        if (tracer) c2 = clock64();
+        if (list_tok != NONE && list_len <= LIGHT_MAX) {
+            // light step, this CTA alone: filter (one thread per posting), then one warp per hit
+            const uint32_t* list = S.wl_pool + __ldcg(S.wl_off + list_tok);
+            __syncthreads();  // sh_qn = 0
+            for (uint32_t i = tid; i < list_len; i += NT) {
+                const uint32_t w = __ldcg(list + i);
+                if (word_has_pair(S, w, a, b)) sh_queue[atomicAdd(&sh_qn, 1u)] = w;  // list_len <= QUEUE_CAP
+            }
+            __syncthreads();
+            matched = sh_qn;
+            if (tracer) c3 = clock64();
+            if (use_cache) {
+                const CacheAdder add{S, H, T};
+                for (uint32_t k = warp; k < matched; k += NT / 32) rewrite_word_warp(S, sh_queue[k], a, b, x, add);
+            } else {
+                const GlobalAdder add{S, LLONG_MAX};
+                for (uint32_t k = warp; k < matched; k += NT / 32) rewrite_word_warp(S, sh_queue[k], a, b, x, add);
+            }
+            for (uint32_t k = tid; k < matched; k += NT) {  // the hits ARE x's posting list
+                if (wl_start + k < S.wl_cap) S.wl_pool[wl_start + k] = sh_queue[k]; else set_status(S.status, ST_LIST_FULL);
+            }
+            __syncthreads();
+            // entries appended during this step: their count comes from the (exact) global table
+            const uint32_t n_now = use_cache ? min(H.n, HC) : 0;
+            for (uint32_t i = first_new_entry + tid; i < n_now; i += NT)
+                if (H.key[i]) H.cnt[i] = __ldcg(S.ph_cnt + H.slot[i]);
+        } else {
+            // heavy step: wake the helper CTAs; counts change behind the cache's back, so reload it afterwards
+            if (tid == 0) {
+                S.ctrl->wl_cursor = wl_start;
+                S.ctrl->n_hot = 0;
+                S.ctrl->cmd = Command{1u, a, b, x, list_tok, list_len, T};
+                __threadfence();
+            }
+            sync_all();
+            if (tracer) c3 = clock64();
+            const Command cmd{1u, a, b, x, list_tok, list_len, T};
+            heavy_rewrite<NT>(S, cmd, n_words, sh_queue, &sh_qn);
+            sync_all();
+            matched = __ldcg(&S.ctrl->wl_cursor) - wl_start;
+            for (uint32_t i = tid; i < n_cached; i += NT)
+                if (H.key[i]) H.cnt[i] = __ldcg(S.ph_cnt + H.slot[i]);
+            const uint32_t n_pending = use_cache ? min(__ldcg(&S.ctrl->n_hot), (unsigned int)S.ph_mask) : 0;  // pairs that rose past T in the heavy step
+            __syncthreads();
+            for (uint32_t i = tid; i < n_pending; i += NT) {
+                const ulonglong2 rec = __ldcg(S.hot + i);
+                if (hc_find(H, rec.x) < 0) hc_append(H, rec.x, (uint32_t)rec.y, __ldcg(S.ph_cnt + (uint32_t)rec.y));
+            }
+            n_heavy++;
+        }
+        if (tracer) c4 = clock64();
+        // ---- close the step ---------------------------------------------------------------------------------------------
+        if (leader) {
+            if (use_cache) {
+                H.cnt[win.slot] = RETIRED;                 // the winner never occurs again (bpe_trainer.py:243);
+                S.ph_cnt[H.slot[win.slot]] = RETIRED;      // a pair without any occurrence is retired the same way
+            } else {
+                S.ph_cnt[win.slot] = RETIRED;
+            }
+            if (matched) S.wl_len[x] = matched;
+            __threadfence();
+        }
         if (matched) {  // bpe_trainer.py:309-316
-            prev_x = x; prev_rank = req ? req - 1 : rmax; prev_matched = matched;
+            wl_cur = wl_start + matched;
             next_id++;
-        } else {        // count > 0 but no occurrence: retired, no merge recorded
-            prev_x = NONE;
+        }
+        __syncthreads();  // cache and leader stores are ordered before the next argmax of this CTA
+        if (tracer) {
+            long long c5 = clock64();
+            S.ctrl->phase_clk[5] += c0a - c0; S.ctrl->phase_clk[6] += c0b - c0a; S.ctrl->phase_clk[7] += c0c - c0b;
+            S.ctrl->phase_clk[0] += c1 - c0; S.ctrl->phase_clk[1] += c2 - c1; S.ctrl->phase_clk[2] += c3 - c2;
+            S.ctrl->phase_clk[3] += c4 - c3; S.ctrl->phase_clk[4] += c5 - c4;
+        }
+        if (S.trace && leader && iter < S.vocab_size) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+            S.trace[4 * iter + 0] = (uint32_t)(now - t_prev); S.trace[4 * iter + 1] = list_len;
+            S.trace[4 * iter + 2] = list_tok == NONE; S.trace[4 * iter + 3] = matched;
+            t_prev = now;
         }
         iter++;
     }
-    if (leader) { S.ctrl->n_iters = iter; S.ctrl->n_merges = next_id - S.first_new_id; }
+    if (tid == 0) {
+        S.ctrl->n_iters = iter; S.ctrl->n_merges = next_id - S.first_new_id; S.ctrl->n_heavy = n_heavy;
+        S.ctrl->cmd.op = 0;
+        __threadfence();
+    }
+    sync_all();  // releases the helpers, which read op = 0 and leave
 }
 
 size_t next_pow2(size_t v) { size_t p = 1; while (p < v) p <<= 1; return p; }
@@ -307,7 +674,7 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     CUDA_TRY(ctx, cudaMemcpyAsync(h_counters, ctx->ut.counters, sizeof(h_counters), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(ctx, cudaStreamSynchronize(s));
     const uint64_t n_unique = h_counters[1], n_sym = h_counters[0];
-    if (n_unique == 0 || n_sym >= 0xFFFFFFF0ull) return ctx_fail(ctx, n_unique ? BPE_ERR_CAPACITY : BPE_ERR_NO_PAIRS, "word table size");
+    if (n_unique == 0 || n_sym + 4 * n_unique >= 0xFFFFFFF0ull) return ctx_fail(ctx, n_unique ? BPE_ERR_CAPACITY : BPE_ERR_NO_PAIRS, "word table size");
     if (vocab_size < first_new_id) vocab_size = first_new_id;  // nothing to learn, but "no pairs" is still an error
 
     cudaEvent_t ev[3];
@@ -324,12 +691,13 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     // one allocation, carved up (all sizes rounded to 256 B)
     struct Part { void** p; size_t bytes; };
     Part parts[] = {
-        {(void**)&S.w_off, n_unique * 4}, {(void**)&S.w_len, n_unique * 4}, {(void**)&S.w_cnt, n_unique * 8}, {(void**)&S.sym, (n_sym + 4) * 4},
-        {(void**)&S.ph_key, ph_cap * 8}, {(void**)&S.ph_cnt, ph_cap * 8}, {(void**)&S.ph_dead, ph_cap}, {(void**)&S.live, ph_cap * 4},
-        {(void**)&S.tk_off, (vocab_size + 2) * 4ull}, {(void**)&S.tk_blob, S.blob_cap}, {(void**)&S.rank, (vocab_size + 1) * 4ull},
+        {(void**)&S.w_off, n_unique * 4}, {(void**)&S.w_len, n_unique * 4}, {(void**)&S.w_cnt, n_unique * 8},
+        {(void**)&S.sym, (n_sym + 4 * n_unique + 8) * 4},
+        {(void**)&S.ph_key, ph_cap * 8}, {(void**)&S.ph_cnt, ph_cap * 8}, {(void**)&S.live, ph_cap * 4}, {(void**)&S.hot, (ph_cap + 1) * 16},
+        {(void**)&S.tk_off, (vocab_size + 2) * 4ull}, {(void**)&S.tk_blob, S.blob_cap}, {(void**)&S.tk_pre, (vocab_size + 1) * 8ull},
         {(void**)&S.wl_off, (vocab_size + 1) * 4ull}, {(void**)&S.wl_len, (vocab_size + 1) * 4ull}, {(void**)&S.wl_pool, (size_t)S.wl_cap * 4},
         {(void**)&S.m_a, (vocab_size + 1) * 4ull}, {(void**)&S.m_b, (vocab_size + 1) * 4ull},
-        {(void**)&S.block_best, sizeof(Best) * 4096}, {(void**)&S.ctrl, sizeof(Ctrl)},
+        {(void**)&S.ctrl, sizeof(Ctrl)}, {(void**)&S.trace, (vocab_size + 1) * 16ull},
     };
     size_t total = 0;
     for (auto& p : parts) total += (p.bytes + 255) / 256 * 256;
@@ -337,24 +705,22 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     if (!base) return BPE_ERR_CUDA;
     size_t at = 0;
     for (auto& p : parts) { *p.p = base + at; at += (p.bytes + 255) / 256 * 256; }
-    // zero the pair table, the control block and the posting lengths
-    CUDA_TRY(ctx, cudaMemsetAsync(S.ph_key, 0, (uint8_t*)S.tk_off - (uint8_t*)S.ph_key, s));
+    if (const char* f = getenv("BPE_B200_TRAIN_FLAGS")) S.flags = (uint32_t)atoi(f);
+    const char* trace_path = getenv("BPE_B200_TRAIN_TRACE");
+    uint32_t* d_trace = S.trace;
+    if (!trace_path) S.trace = nullptr;
+    // zero the pair table (keys, counts), the posting offsets / lengths and the control block
+    CUDA_TRY(ctx, cudaMemsetAsync(S.ph_key, 0, (uint8_t*)S.live - (uint8_t*)S.ph_key, s));
     CUDA_TRY(ctx, cudaMemsetAsync(S.wl_off, 0, (uint8_t*)S.wl_pool - (uint8_t*)S.wl_off, s));
     CUDA_TRY(ctx, cudaMemsetAsync(S.ctrl, 0, sizeof(Ctrl), s));
 
-    // initial tokens: bytes, offsets, lexicographic ranks (equal byte strings share a rank)
-    std::vector<uint32_t> order(first_new_id), rank(first_new_id);
-    for (uint32_t i = 0; i < first_new_id; i++) order[i] = i;
-    auto tok = [&](uint32_t t) { return std::string((const char*)h_init_blob + h_init_off[t], h_init_off[t + 1] - h_init_off[t]); };
-    std::sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return tok(x) < tok(y); });
-    uint32_t r = 0;
-    for (uint32_t i = 0; i < first_new_id; i++) {
-        if (i && tok(order[i]) != tok(order[i - 1])) r++;
-        rank[order[i]] = r;
-    }
+    // initial tokens: bytes, offsets, prefix keys
+    std::vector<unsigned long long> pre(first_new_id, 0);
+    for (uint32_t t = 0; t < first_new_id; t++)
+        for (uint32_t i = 0; i < 8; i++) pre[t] = (pre[t] << 8) | (i < h_init_off[t + 1] - h_init_off[t] ? h_init_blob[h_init_off[t] + i] : 0u);
     CUDA_TRY(ctx, cudaMemcpyAsync(S.tk_blob, h_init_blob, init_bytes, cudaMemcpyHostToDevice, s));
     CUDA_TRY(ctx, cudaMemcpyAsync(S.tk_off, h_init_off, (first_new_id + 1) * 4ull, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(ctx, cudaMemcpyAsync(S.rank, rank.data(), first_new_id * 4ull, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(ctx, cudaMemcpyAsync(S.tk_pre, pre.data(), first_new_id * 8ull, cudaMemcpyHostToDevice, s));
 
     {
         KernelTimer t(ctx, "words_build_kernel", s);
@@ -383,21 +749,43 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
         return BPE_OK;
     }
 
-    int per_sm = 0;
-    CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, merge_loop_kernel, TRAIN_THREADS, 0));
-    cudaDeviceProp prop;
-    CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, ctx->device));
-    int grid = prop.multiProcessorCount * (per_sm > 2 ? 2 : per_sm);
-    if (grid > 4096) grid = 4096;
-    // small problems: fewer CTAs make the grid barrier cheaper
-    uint64_t work = std::max<uint64_t>(h_ctrl.n_live, n_words);
-    int want = (int)std::min<uint64_t>((work + TRAIN_THREADS - 1) / TRAIN_THREADS, (uint64_t)grid);
-    if (want < 1) want = 1;
-    grid = want;
-    {
+    // One cluster with the hardware barrier while the word table is small enough to be swept by ~16k threads in a few
+    // microseconds; a cooperative grid beyond that.
+    bool launched = false;
+    const char* mode = getenv("BPE_B200_TRAIN_MODE");  // "grid" / "cluster" force a variant (experiments, tests)
+    if (!(mode && !strcmp(mode, "grid")) && (n_words <= (4u << 20) || (mode && !strcmp(mode, "cluster")))) {
+        auto kern = merge_loop_kernel<true, 1024>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HotCache));
+        for (int csize = 16; csize >= 8 && !launched && e == cudaSuccess; csize -= 8) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(csize); cfg.blockDim = dim3(1024); cfg.dynamicSmemBytes = sizeof(HotCache); cfg.stream = s;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = csize; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            int n_clusters = 0;
+            if (cudaOccupancyMaxActiveClusters(&n_clusters, kern, &cfg) != cudaSuccess || n_clusters < 1) { cudaGetLastError(); continue; }
+            KernelTimer t(ctx, "merge_loop_kernel", s);
+            if (cudaLaunchKernelEx(&cfg, kern, S) == cudaSuccess) launched = true; else cudaGetLastError();
+        }
+    }
+    if (!launched) {
+        auto kern = merge_loop_kernel<false, 512>;
+        int per_sm = 0;
+        CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HotCache)));
+        CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 512, sizeof(HotCache)));
+        cudaDeviceProp prop;
+        CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, ctx->device));
+        int grid = prop.multiProcessorCount * (per_sm > 1 ? 1 : per_sm);
+        grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n_words + 511) / 512, (uint64_t)grid));
+        if (const char* env = getenv("BPE_B200_TRAIN_CTAS")) {
+            int v = atoi(env);
+            if (v >= 1 && v <= prop.multiProcessorCount * per_sm) grid = v;
+        }
         KernelTimer t(ctx, "merge_loop_kernel", s);
         void* args[] = {&S};
-        CUDA_TRY(ctx, cudaLaunchCooperativeKernel((void*)merge_loop_kernel, dim3(grid), dim3(TRAIN_THREADS), args, 0, s));
+        CUDA_TRY(ctx, cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(512), args, sizeof(HotCache), s));
     }
     CUDA_TRY(ctx, cudaMemcpyAsync(&h_ctrl, S.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, s));
     cudaEventRecord(ev[2], s);
@@ -407,6 +795,17 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     CUDA_TRY(ctx, cudaMemcpyAsync(h_merge_b, S.m_b, learned * 4ull, cudaMemcpyDeviceToHost, s));
     CUDA_TRY(ctx, cudaStreamSynchronize(s));
     *n_merges = learned;
+    if (trace_path) {  // developer aid: per-iteration timings of the loop
+        fprintf(stderr, "[train trace] driver thread 0 cycles: argmax %llu, select+bookkeeping %llu, filter/wake %llu, rewrite %llu, close %llu; "
+                        "[argmax: scan %llu, warp reduce %llu, barrier %llu] rebuilds %u, heavy steps %u\n", h_ctrl.phase_clk[0], h_ctrl.phase_clk[1], h_ctrl.phase_clk[2], h_ctrl.phase_clk[3],
+                h_ctrl.phase_clk[4], h_ctrl.phase_clk[5], h_ctrl.phase_clk[6], h_ctrl.phase_clk[7], h_ctrl.n_rebuilds, h_ctrl.n_heavy);
+        std::vector<uint32_t> tr(4ull * h_ctrl.n_iters);
+        cudaMemcpy(tr.data(), d_trace, tr.size() * 4, cudaMemcpyDeviceToHost);
+        if (FILE* f = fopen(trace_path, "w")) {
+            for (uint32_t k = 0; k < h_ctrl.n_iters && k < vocab_size; k++) fprintf(f, "%u %u %u %u\n", tr[4 * k], tr[4 * k + 1], tr[4 * k + 2], tr[4 * k + 3]);
+            fclose(f);
+        }
+    }
     float ms0 = 0, ms1 = 0;
     cudaEventElapsedTime(&ms0, ev[0], ev[1]);
     cudaEventElapsedTime(&ms1, ev[1], ev[2]);
