@@ -43,6 +43,7 @@ int ctx_status_to_code(bpe_ctx* ctx, uint32_t st) {
     if (st & ST_TABLE_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "pretoken table full (bpe_ctx_configure: table_log2)");
     if (st & ST_POOL_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "pretoken byte / id pool full (bpe_ctx_configure: pool_bytes)");
     if (st & ST_PAIR_TABLE_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "pair table full");
+    if (st & ST_WATCHDOG) return ctx_fail(ctx, BPE_ERR_CUDA, "merge loop watchdog: no progress for 60 s (internal error)");
     if (st & ST_LIST_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "posting pool / token byte pool full");
     return ctx_fail(ctx, BPE_ERR_CUDA, "unknown status bits");
 }

@@ -19,6 +19,7 @@ enum : uint32_t {
     ST_MISSING_ID = 1u << 4,
     ST_PAIR_TABLE_FULL = 1u << 5,
     ST_LIST_FULL = 1u << 6,
+    ST_WATCHDOG = 1u << 7,
 };
 
 // ---- code-point classes (include/bpe_unicode_tables.h) --------------------------------------------------

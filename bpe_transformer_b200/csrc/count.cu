@@ -13,7 +13,7 @@
 // HBM traffic: N bytes of text + N/8 of mask read; the tables stay in shared memory / L2.
 #include "common.cuh"
 
-#define COUNT_THREADS 512
+#define COUNT_THREADS 1024
 #define COUNT_SLOTS 4096  // per-CTA shared table: 8 B key + 4 B count + 4 B position + 4 B length = 20 B/slot = 80 KB
 #define COUNT_PROBES 8
 
@@ -36,6 +36,8 @@ struct SharedTable {
     uint32_t len[COUNT_SLOTS];
 };
 
+#define COUNT_SMEM (sizeof(SharedTable) + (COUNT_THREADS / 32) * 1056 * sizeof(unsigned short))
+
 __device__ __forceinline__ bool token_is_special(const Specials& sp, const uint8_t* __restrict__ text, uint64_t p, uint64_t len) {
     uint8_t b0 = text[p];
     if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return false;
@@ -48,9 +50,26 @@ __device__ __forceinline__ bool token_is_special(const Specials& sp, const uint8
     return false;
 }
 
+// Key only (the check word is recomputed when a shared-table entry is folded into the global table).
+__device__ __forceinline__ uint64_t hash_key(const uint8_t* __restrict__ base, uint64_t p, uint32_t len) {
+    uint64_t h = 0x243F6A8885A308D3ull ^ ((uint64_t)len * 0x9E3779B97F4A7C15ull);
+    uint32_t o = 0;
+    for (; o + 8 <= len; o += 8) h = mix64(h, load_u64_unaligned(base, p + o));
+    if (o < len) h = mix64(h, load_u64_unaligned(base, p + o) & ((1ull << ((len - o) * 8)) - 1ull));
+    h ^= h >> 29;
+    return h ? h : 1ull;
+}
+
+// A warp takes 32 mask words (1 KiB of text) per round.  The set bits of the 32 words are spread evenly over the
+// lanes — lane L takes tokens L, L + 32, ... of the 1 KiB — through a per-warp list of start positions in shared
+// memory, so that every lane hashes and counts one token at a time instead of looping over "its" 32 bytes (token
+// counts per 32 bytes vary a lot: that loop ran with ~6 of 32 lanes active).
 __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams P, const __grid_constant__ Specials sp) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SharedTable& st = *reinterpret_cast<SharedTable*>(smem_raw);
+    unsigned short* pos_all = reinterpret_cast<unsigned short*>(smem_raw + sizeof(SharedTable));
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned short* pos = pos_all + warp * 1056;  // 1024 starts + 1 end marker, padded
     for (uint32_t k = threadIdx.x; k < COUNT_SLOTS; k += COUNT_THREADS) { st.key[k] = 0; st.cnt[k] = 0; }
     __syncthreads();
 
@@ -59,39 +78,59 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
     const uint64_t base = w_lo * 32;  // first byte of this CTA's range
     uint64_t local_tokens = 0;
 
-    for (uint64_t wi = w_lo + threadIdx.x; wi < w_hi; wi += COUNT_THREADS) {
-        uint32_t w = __ldg(P.start + wi);
-        for (uint32_t m = w; m; m &= m - 1) {
-            uint32_t b = __ffs(m) - 1;
-            uint64_t p = wi * 32 + b;
-            uint64_t e = token_end(P.start, P.n_words, wi, w, b, P.n);
-            uint64_t len = e - p;
+    for (uint64_t w0 = w_lo + warp * 32; w0 < w_hi; w0 += COUNT_THREADS) {  // COUNT_THREADS = 32 words x warps per CTA
+        const uint64_t wi = w0 + lane;
+        const uint32_t w = wi < w_hi ? __ldg(P.start + wi) : 0u;
+        // exclusive scan of the per-lane token counts
+        const uint32_t mine = __popc(w);
+        uint32_t incl = mine;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= (uint32_t)o) incl += y;
+        }
+        const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        if (total == 0) continue;
+        uint32_t at = incl - mine;
+        for (uint32_t m = w; m; m &= m - 1) pos[at++] = (unsigned short)(lane * 32 + (__ffs(m) - 1));
+        // end of the last token: the next set bit anywhere behind this KiB
+        uint32_t last_lane = 31 - __clz(__ballot_sync(0xFFFFFFFFu, w != 0));
+        uint64_t tail_end = 0;
+        if (lane == last_lane) tail_end = token_end(P.start, P.n_words, wi, w, 31 - __clz(w), P.n);
+        tail_end = __shfl_sync(0xFFFFFFFFu, tail_end, last_lane);
+        __syncwarp();
+        const uint64_t kib = w0 * 32;
+        for (uint32_t t = lane; t < total; t += 32) {
+            const uint64_t p = kib + pos[t];
+            const uint64_t e = (t + 1 < total) ? kib + pos[t + 1] : tail_end;
+            const uint64_t len = e - p;
             if (sp.n && token_is_special(sp, P.text, p, len)) continue;
-            TokenKey k = hash_bytes(P.text, p, len);
             local_tokens++;
             bool done = false;
+            uint64_t key;
             if (len < 0xFFFFFFFFull && p - base < 0xFFFFFFFFull) {
-                uint32_t slot = (uint32_t)(k.key >> 40) & (COUNT_SLOTS - 1);
+                key = hash_key(P.text, p, (uint32_t)len);
+                uint32_t slot = (uint32_t)(key >> 40) & (COUNT_SLOTS - 1);
 #pragma unroll 1
                 for (int probe = 0; probe < COUNT_PROBES && !done; probe++) {
                     unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&st.key[slot]);
                     if (cur == 0) {
-                        cur = atomicCAS(&st.key[slot], 0ull, (unsigned long long)k.key);
+                        cur = atomicCAS(&st.key[slot], 0ull, (unsigned long long)key);
                         if (cur == 0) {
                             st.pos[slot] = (uint32_t)(p - base);
                             st.len[slot] = (uint32_t)len;
-                            cur = k.key;
+                            cur = key;
                         }
                     }
-                    if (cur == k.key) {
+                    if (cur == key) {
                         atomicAdd(&st.cnt[slot], 1u);
                         done = true;
                     }
                     slot = (slot + 1) & (COUNT_SLOTS - 1);
                 }
             }
-            if (!done) unique_insert(P.ut, P.status, P.text, p, (uint32_t)len, k, 1);
+            if (!done) unique_insert(P.ut, P.status, P.text, p, (uint32_t)len, hash_bytes(P.text, p, len), 1);
         }
+        __syncwarp();
     }
     __syncthreads();
     // fold the CTA's table into the context's table
@@ -99,7 +138,7 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
         if (st.key[s] == 0) continue;
         uint64_t p = base + st.pos[s];
         uint32_t len = st.len[s];
-        TokenKey k = hash_bytes(P.text, p, len);  // recomputes the check word (not kept in shared memory)
+        TokenKey k = hash_bytes(P.text, p, len);  // key again, plus the check word (not kept in shared memory)
         unique_insert(P.ut, P.status, P.text, p, len, k, st.cnt[s]);
     }
     // total occurrences (block-reduced)
@@ -139,7 +178,7 @@ int launch_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t
     CountParams P;
     P.text = d_text; P.n = n; P.start = d_start; P.status = ctx->d_status; P.ut = ctx->ut;
     P.n_words = (n + 31) / 32;
-    uint64_t grid = (uint64_t)BPE_N_SM * 2;
+    uint64_t grid = (uint64_t)BPE_N_SM;  // one CTA of 32 warps per SM (the shared table and the start lists take 144 KB)
     // keep ranges a multiple of the CTA width so that all threads stay busy; small inputs use fewer CTAs
     uint64_t per = (P.n_words + grid - 1) / grid;
     per = (per + COUNT_THREADS - 1) / COUNT_THREADS * COUNT_THREADS;
@@ -147,11 +186,11 @@ int launch_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t
     P.words_per_block = per;
     static bool attr_set = false;
     if (!attr_set) {
-        CUDA_TRY(ctx, cudaFuncSetAttribute(count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SharedTable)));
+        CUDA_TRY(ctx, cudaFuncSetAttribute(count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)COUNT_SMEM));
         attr_set = true;
     }
     KernelTimer t(ctx, "count_kernel", s);
-    count_kernel<<<(unsigned)grid, COUNT_THREADS, sizeof(SharedTable), s>>>(P, ctx->sp);
+    count_kernel<<<(unsigned)grid, COUNT_THREADS, COUNT_SMEM, s>>>(P, ctx->sp);
     CUDA_TRY(ctx, cudaGetLastError());
     return BPE_OK;
 }

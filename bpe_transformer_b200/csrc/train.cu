@@ -27,10 +27,12 @@
 #include <cooperative_groups.h>
 
 #include <algorithm>
+#include <chrono>
 #include <climits>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 
 #include "common.cuh"
 
@@ -68,6 +70,7 @@ struct Ctrl {
     unsigned int n_heavy;
     unsigned int pad;
     Command cmd;
+    unsigned int dbg[8];      // flags bit 1: [0] stale cache copies, [1] first iteration with one, [2] hot pairs missing from the cache, [3] first iteration
     unsigned long long phase_clk[8];  // developer trace: SM cycles of the driver's thread 0 per phase, summed over iterations
 };
 
@@ -85,6 +88,8 @@ struct TrainState {
     uint32_t* status;
     uint32_t first_new_id, vocab_size;
     uint32_t flags;  // bit 0: never use the shared-memory cache (experiments)
+    uint32_t watchdog_s;
+    volatile uint32_t* beat;  // pinned host memory: [2 * cta] = iteration, [2 * cta + 1] = phase (what the host prints if the loop stalls)
 };
 
 // Slot of pair `key` in the global table, inserted on first sight (compare-and-swap first: one round trip for a new pair).
@@ -145,12 +150,13 @@ __device__ __forceinline__ uint32_t hc_hash(unsigned long long key) { return (ui
 
 __device__ __forceinline__ int hc_find(const HotCache& H, unsigned long long key) {
     uint32_t h = hc_hash(key) & (HIDX - 1);
-    for (;;) {
+    for (uint32_t probe = 0; probe < HIDX; probe++) {
         unsigned int v = *reinterpret_cast<const volatile unsigned short*>(&H.index[h]);
         if (v == 0) return -1;
         if (H.key[v - 1] == key) return (int)v - 1;
         h = (h + 1) & (HIDX - 1);
     }
+    return -1;
 }
 
 // Appends (key, slot) with count `cnt`; a concurrent duplicate loses and becomes a hole.
@@ -160,7 +166,7 @@ __device__ __forceinline__ void hc_append(HotCache& H, unsigned long long key, u
     H.key[idx] = key; H.slot[idx] = slot; H.cnt[idx] = cnt;
     __threadfence_block();
     uint32_t h = hc_hash(key) & (HIDX - 1);
-    for (;;) {
+    for (uint32_t probe = 0; probe < HIDX; probe++) {
         unsigned short v = *reinterpret_cast<volatile unsigned short*>(&H.index[h]);
         if (v == 0) {
             v = atomicCAS(&H.index[h], (unsigned short)0, (unsigned short)(idx + 1));
@@ -402,13 +408,16 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
     __shared__ int sh_bit;
     __shared__ unsigned int sh_above;
     __shared__ Command sh_cmd;
+    __shared__ bool sh_stop;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_words = S.ctrl->n_words;
 
     if (blockIdx.x != 0) {  // helper CTAs: asleep on the barrier until the driver broadcasts a heavy step
-        for (;;) {
+        for (uint32_t round = 0;; round++) {
+            if (tid == 0) { S.beat[2 * blockIdx.x] = round; S.beat[2 * blockIdx.x + 1] = 20; }
             sync_all();
             if (tid == 0) {
+                S.beat[2 * blockIdx.x + 1] = 21;
                 const volatile Command* c = &S.ctrl->cmd;
                 sh_cmd.op = c->op; sh_cmd.a = c->a; sh_cmd.b = c->b; sh_cmd.x = c->x; sh_cmd.list_tok = c->list_tok;
                 sh_cmd.list_len = c->list_len; sh_cmd.threshold = c->threshold;
@@ -417,6 +426,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             const Command cmd = sh_cmd;
             if (cmd.op == 0) return;
             heavy_rewrite<NT>(S, cmd, n_words, sh_queue, &sh_qn);
+            if (tid == 0) S.beat[2 * blockIdx.x + 1] = 22;
             sync_all();
         }
     }
@@ -432,12 +442,27 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
     unsigned long long t_prev = 0;
     if (S.trace && leader) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_prev));
 
+    unsigned long long t_start;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_start));
+    uint32_t passes = 0;
     while (next_id < S.vocab_size) {
+        if ((++passes & 255u) == 0) {  // watchdog: a bug must not hang the GPU (default 120 s, far beyond any real training)
+            if (tid == 0) {            // one thread decides, so that the whole CTA leaves together
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                sh_stop = now - t_start > (unsigned long long)S.watchdog_s * 1000000000ull && now - t_start < (1ull << 62);
+                if (sh_stop) { set_status(S.status, ST_WATCHDOG); S.ctrl->dbg[4] = iter; S.ctrl->dbg[5] = passes; }
+            }
+            __syncthreads();
+            if (sh_stop) break;
+        }
         // Cache invariant: every pair with count >= T has an entry (pairs are appended when their count rises past T;
         // leftovers below T and holes are allowed).  If the best entry has count >= T it is the global argmax;
         // otherwise T is lowered and the cache rebuilt from a log2 histogram of all counts.
+        if (tid == 0) { S.beat[0] = iter; S.beat[1] = need_rebuild ? 1 : 2; }
         if (need_rebuild && use_cache) {
             if (++spins > 64) { if (tid == 0) set_status(S.status, ST_PAIR_TABLE_FULL); break; }
+            __syncthreads();  // every thread has read H.n / the winner that sent it here before the cache is wiped
             if (tid < 64) sh_hist[tid] = 0;
             for (uint32_t k = tid; k < HIDX; k += NT) H.index[k] = 0;
             if (tid == 0) H.n = 0;
@@ -491,6 +516,21 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         }
         if (!use_cache) T = LLONG_MAX;  // GlobalAdder never reports crossings
 
+        if ((S.flags & 2u) && use_cache) {  // self-check (experiments): the cache against the global table
+            const uint32_t n_c = min(H.n, HC);
+            for (uint32_t i = tid; i < n_c; i += NT)
+                if (H.key[i] && H.cnt[i] != __ldcg(S.ph_cnt + H.slot[i])) {
+                    if (atomicAdd(&S.ctrl->dbg[0], 1u) == 0) S.ctrl->dbg[1] = iter;
+                }
+            const uint32_t n_all = __ldcg(&S.ctrl->n_live);
+            for (uint32_t i = tid; i < n_all; i += NT) {
+                uint32_t slot = __ldcg(S.live + i);
+                if (__ldcg(S.ph_cnt + slot) >= T && hc_find(H, __ldcg(S.ph_key + slot)) < 0) {
+                    if (atomicAdd(&S.ctrl->dbg[2], 1u) == 0) S.ctrl->dbg[3] = iter;
+                }
+            }
+            __syncthreads();
+        }
         // ---- argmax over the cached pairs of (count, bytes(a), bytes(b)): shared memory only -------------------------------
         long long c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0;
         if (tracer) c0 = clock64();
@@ -551,6 +591,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             uint32_t lb = __ldcg(S.wl_len + b);
             if (list_tok == NONE || lb < list_len) { list_tok = b; list_len = lb; }
         }
+        if (tid == 0) S.beat[1] = 3;
         const uint32_t wl_start = wl_cur;
         const uint32_t first_new_entry = n_cached;
         uint32_t matched = 0;
@@ -582,6 +623,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             }
             __syncthreads();
             matched = sh_qn;
+            if (tid == 0) S.beat[1] = 5;
             if (tracer) c3 = clock64();
             if (use_cache) {
                 const CacheAdder add{S, H, T};
@@ -593,6 +635,8 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             for (uint32_t k = tid; k < matched; k += NT) {  // the hits ARE x's posting list
                 if (wl_start + k < S.wl_cap) S.wl_pool[wl_start + k] = sh_queue[k]; else set_status(S.status, ST_LIST_FULL);
             }
+            if (tid == 0) S.beat[1] = 6;
+            __threadfence();  // the count updates were posted without waiting: they must have landed before the reload below
             __syncthreads();
             // entries appended during this step: their count comes from the (exact) global table
             const uint32_t n_now = use_cache ? min(H.n, HC) : 0;
@@ -605,12 +649,16 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
                 S.ctrl->n_hot = 0;
                 S.ctrl->cmd = Command{1u, a, b, x, list_tok, list_len, T};
                 __threadfence();
+                S.beat[1] = 7;
             }
             sync_all();
+            if (tid == 0) S.beat[1] = 8;
             if (tracer) c3 = clock64();
             const Command cmd{1u, a, b, x, list_tok, list_len, T};
             heavy_rewrite<NT>(S, cmd, n_words, sh_queue, &sh_qn);
+            if (tid == 0) S.beat[1] = 9;
             sync_all();
+            if (tid == 0) S.beat[1] = 10;
             matched = __ldcg(&S.ctrl->wl_cursor) - wl_start;
             for (uint32_t i = tid; i < n_cached; i += NT)
                 if (H.key[i]) H.cnt[i] = __ldcg(S.ph_cnt + H.slot[i]);
@@ -624,6 +672,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         }
         if (tracer) c4 = clock64();
         // ---- close the step ---------------------------------------------------------------------------------------------
+        if (tid == 0) S.beat[1] = 11;
         if (leader) {
             if (use_cache) {
                 H.cnt[win.slot] = RETIRED;                 // the winner never occurs again (bpe_trainer.py:243);
@@ -658,6 +707,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         S.ctrl->n_iters = iter; S.ctrl->n_merges = next_id - S.first_new_id; S.ctrl->n_heavy = n_heavy;
         S.ctrl->cmd.op = 0;
         __threadfence();
+        S.beat[1] = 12;
     }
     sync_all();  // releases the helpers, which read op = 0 and leave
 }
@@ -706,6 +756,8 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     size_t at = 0;
     for (auto& p : parts) { *p.p = base + at; at += (p.bytes + 255) / 256 * 256; }
     if (const char* f = getenv("BPE_B200_TRAIN_FLAGS")) S.flags = (uint32_t)atoi(f);
+    S.watchdog_s = 120;
+    if (const char* f = getenv("BPE_B200_TRAIN_WATCHDOG")) S.watchdog_s = (uint32_t)std::max(1, atoi(f));
     const char* trace_path = getenv("BPE_B200_TRAIN_TRACE");
     uint32_t* d_trace = S.trace;
     if (!trace_path) S.trace = nullptr;
@@ -749,6 +801,14 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
         return BPE_OK;
     }
 
+    // Progress words in pinned host memory: if the loop ever stalls the host says where instead of hanging silently.
+    static uint32_t* h_beat = nullptr;
+    if (!h_beat) CUDA_TRY(ctx, cudaHostAlloc((void**)&h_beat, 2 * 4096 * sizeof(uint32_t), cudaHostAllocMapped));
+    memset(h_beat, 0, 2 * 4096 * sizeof(uint32_t));
+    uint32_t* d_beat = nullptr;
+    CUDA_TRY(ctx, cudaHostGetDevicePointer((void**)&d_beat, h_beat, 0));
+    S.beat = d_beat;
+    int launched_ctas = 0;
     // One cluster with the hardware barrier while the word table is small enough to be swept by ~16k threads in a few
     // microseconds; a cooperative grid beyond that.
     bool launched = false;
@@ -767,7 +827,7 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
             int n_clusters = 0;
             if (cudaOccupancyMaxActiveClusters(&n_clusters, kern, &cfg) != cudaSuccess || n_clusters < 1) { cudaGetLastError(); continue; }
             KernelTimer t(ctx, "merge_loop_kernel", s);
-            if (cudaLaunchKernelEx(&cfg, kern, S) == cudaSuccess) launched = true; else cudaGetLastError();
+            if (cudaLaunchKernelEx(&cfg, kern, S) == cudaSuccess) { launched = true; launched_ctas = csize; } else cudaGetLastError();
         }
     }
     if (!launched) {
@@ -786,6 +846,25 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
         KernelTimer t(ctx, "merge_loop_kernel", s);
         void* args[] = {&S};
         CUDA_TRY(ctx, cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(512), args, sizeof(HotCache), s));
+        launched_ctas = grid;
+    }
+    {   // wait with a deadline
+        cudaEvent_t done;
+        cudaEventCreateWithFlags(&done, cudaEventDisableTiming);
+        cudaEventRecord(done, s);
+        auto t0 = std::chrono::steady_clock::now();
+        while (cudaEventQuery(done) == cudaErrorNotReady) {
+            double waited = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            if (waited > S.watchdog_s + 10.0) {
+                fprintf(stderr, "[bpe_train] merge loop stalled: driver at iteration %u phase %u;", h_beat[0], h_beat[1]);
+                for (int c = 1; c < launched_ctas && c < 16; c++) fprintf(stderr, " cta%d round %u phase %u;", c, h_beat[2 * c], h_beat[2 * c + 1]);
+                fprintf(stderr, "\n");
+                cudaEventDestroy(done);
+                return ctx_fail(ctx, BPE_ERR_CUDA, "merge loop stalled (internal error); the process must exit");
+            }
+            if (waited > 0.002) std::this_thread::sleep_for(std::chrono::microseconds(200));
+        }
+        cudaEventDestroy(done);
     }
     CUDA_TRY(ctx, cudaMemcpyAsync(&h_ctrl, S.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, s));
     cudaEventRecord(ev[2], s);
@@ -795,6 +874,12 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     CUDA_TRY(ctx, cudaMemcpyAsync(h_merge_b, S.m_b, learned * 4ull, cudaMemcpyDeviceToHost, s));
     CUDA_TRY(ctx, cudaStreamSynchronize(s));
     *n_merges = learned;
+    if (h_ctrl.dbg[5])
+        fprintf(stderr, "[train watchdog] stopped at iteration %u after %u loop passes; merges %u, rebuilds %u, heavy %u\n", h_ctrl.dbg[4], h_ctrl.dbg[5],
+                h_ctrl.n_merges, h_ctrl.n_rebuilds, h_ctrl.n_heavy);
+    if (S.flags & 2u)
+        fprintf(stderr, "[train check] stale cache copies %u (first at iteration %u), hot pairs missing from the cache %u (first at iteration %u), rebuilds %u, heavy %u, iterations %u\n",
+                h_ctrl.dbg[0], h_ctrl.dbg[1], h_ctrl.dbg[2], h_ctrl.dbg[3], h_ctrl.n_rebuilds, h_ctrl.n_heavy, h_ctrl.n_iters);
     if (trace_path) {  // developer aid: per-iteration timings of the loop
         fprintf(stderr, "[train trace] driver thread 0 cycles: argmax %llu, select+bookkeeping %llu, filter/wake %llu, rewrite %llu, close %llu; "
                         "[argmax: scan %llu, warp reduce %llu, barrier %llu] rebuilds %u, heavy steps %u\n", h_ctrl.phase_clk[0], h_ctrl.phase_clk[1], h_ctrl.phase_clk[2], h_ctrl.phase_clk[3],
