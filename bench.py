@@ -211,7 +211,6 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
     from bpe_transformer_b200 import _lib, train_bpe
     from bpe_transformer_b200 import distributed as D
     from bpe_transformer_b200.tokenization import BPETokenizer, BPETrainer
-    from bpe_transformer_b200.tokenization.preprocessing.pretokenization import read_file_pinned
 
     path = corpus_path(args.bytes)
     if rank == 0:
@@ -240,16 +239,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
     # ---- this rank's shard, resident in HBM ------------------------------------------------------------------
     offs = D.shard_offsets(path, world, specials) if world > 1 else [0, total]
     lo, hi = offs[rank], offs[rank + 1]
-    if world == 1:
-        host = read_file_pinned(path)
-    else:
-        host = torch.empty(hi - lo, dtype=torch.uint8, pin_memory=True)
-        with open(path, "rb", buffering=0) as fh:
-            fh.seek(lo)
-            view, got = memoryview(host.numpy()), 0
-            while got < hi - lo:
-                got += fh.readinto(view[got:])
-    d_text, n_local = eng.to_device(host)
+    d_text, n_local = eng.load_file(path, lo, hi)
     torch.cuda.synchronize()
     eng.set_special_tokens(_lib.sort_specials(specials))
 
@@ -308,13 +298,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
     if world > 1:
         # encode shards are cut at line ends, not at document ends: reload this rank's lines
         llo, lhi = line_offs[rank], line_offs[rank + 1]
-        host_e = torch.empty(lhi - llo, dtype=torch.uint8, pin_memory=True)
-        with open(path, "rb", buffering=0) as fh:
-            fh.seek(llo)
-            view, got = memoryview(host_e.numpy()), 0
-            while got < lhi - llo:
-                got += fh.readinto(view[got:])
-        d_enc, n_enc = eng.to_device(host_e)
+        d_enc, n_enc = eng.load_file(path, llo, lhi)
     else:
         d_enc, n_enc = d_text, n_local
     torch.cuda.synchronize()

@@ -25,7 +25,7 @@ SYMBOLS = [
     "bpe_ctx_create", "bpe_ctx_destroy", "bpe_last_error", "bpe_ctx_configure", "bpe_set_special_tokens", "bpe_scan",
     "bpe_count", "bpe_unique_stats", "bpe_unique_export", "bpe_unique_import", "bpe_unique_reset", "bpe_train",
     "bpe_train_timing", "bpe_load_model", "bpe_encode", "bpe_decode", "bpe_kernel_times", "bpe_set_profiling",
-    "bpe_decode_noalloc",
+    "bpe_decode_noalloc", "bpe_load_file", "bpe_store_to_host",
 ]
 
 
@@ -79,6 +79,8 @@ def load_library():
         lib.bpe_decode.argtypes = [vp, vp, C.c_int, C.c_uint64, u8p, u64p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_uint64), vp]
         lib.bpe_decode_noalloc.argtypes = [vp, C.c_int, C.c_uint64, u8p, u64p, C.c_uint32, u8p, C.c_uint64, C.POINTER(C.c_uint64), vp,
                                            C.c_char_p, C.c_size_t]
+        lib.bpe_load_file.argtypes = [vp, C.c_char_p, C.c_uint64, C.c_uint64, u8p, vp]
+        lib.bpe_store_to_host.argtypes = [vp, vp, C.c_uint64, vp, vp]
         lib.bpe_kernel_times.argtypes = [vp, C.POINTER(KernelTime), C.c_int]
         lib.bpe_set_profiling.argtypes = [vp, C.c_int]
         for name in SYMBOLS:
@@ -174,6 +176,25 @@ class Engine:
         if n:
             dev[:n].copy_(host, non_blocking=True)
         return dev, n
+
+    def load_file(self, path, lo: int = 0, hi: int | None = None) -> tuple["object", int]:
+        """Bytes [lo, hi) of a file -> padded device tensor and its length (threaded reads through pinned staging)."""
+        torch = self.torch
+        size = os.path.getsize(path)  # FileNotFoundError like open()
+        hi = size if hi is None else min(hi, size)
+        n = max(0, hi - lo)
+        dev = torch.empty(n + TEXT_PAD, dtype=torch.uint8, device=f"cuda:{self.device}")
+        if n:
+            self._check(self.lib.bpe_load_file(self.ctx, os.fsencode(path), lo, n, dev.data_ptr(), self._stream()))
+        return dev, n
+
+    def to_host_array(self, d_tensor, dtype) -> np.ndarray:
+        """Device tensor -> new NumPy array of `dtype` (same bytes), through the pinned staging buffers."""
+        nbytes = int(d_tensor.numel()) * d_tensor.element_size()
+        out = np.empty(nbytes // np.dtype(dtype).itemsize, dtype=dtype)
+        if nbytes:
+            self._check(self.lib.bpe_store_to_host(self.ctx, d_tensor.data_ptr(), nbytes, out.ctypes.data_as(C.c_void_p), self._stream()))
+        return out
 
     def new_mask(self, n: int):
         return self.torch.empty(n // 32 + 2, dtype=self.torch.int32, device=f"cuda:{self.device}")

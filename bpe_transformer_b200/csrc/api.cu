@@ -112,6 +112,7 @@ void bpe_ctx_destroy(bpe_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     free_unique(ctx);
+    io_staging_free(ctx);
     cudaFree(ctx->d_status); cudaFree(ctx->d_stage1); cudaFree(ctx->d_stage2);
     cudaFree(ctx->d_mkey); cudaFree(ctx->d_mrank); cudaFree(ctx->d_mid); cudaFree(ctx->d_byte_to_id); cudaFree(ctx->d_special_id);
     cudaFree(ctx->d_idpool);

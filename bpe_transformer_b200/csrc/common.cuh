@@ -224,6 +224,7 @@ struct bpe_ctx {
     // scratch reused across calls
     void* scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    void* io_staging = nullptr;  // io.cu: pinned staging buffers + copy stream
     // timing
     bool profiling = false;
     std::vector<bpe_kernel_time> times;
@@ -269,6 +270,8 @@ struct KernelTimer {
         ctx->times.push_back({name, (double)ms, 1});
     }
 };
+
+void io_staging_free(bpe_ctx* ctx);
 
 // kernels launched from api.cu, defined in the other translation units
 int launch_scan(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_cutmask, uint32_t flags, uint32_t* d_start, cudaStream_t s);

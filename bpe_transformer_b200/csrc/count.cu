@@ -14,7 +14,7 @@
 #include "common.cuh"
 
 #define COUNT_THREADS 1024
-#define COUNT_SLOTS 4096  // per-CTA shared table: 8 B key + 4 B count + 4 B position + 4 B length = 20 B/slot = 80 KB
+#define COUNT_SLOTS 8192  // per-CTA shared table: 8 B key + 4 B count + 4 B position = 16 B/slot = 128 KB
 #define COUNT_PROBES 8
 
 namespace {
@@ -32,20 +32,53 @@ struct CountParams {
 struct SharedTable {
     unsigned long long key[COUNT_SLOTS];
     uint32_t cnt[COUNT_SLOTS];
-    uint32_t pos[COUNT_SLOTS];  // byte position relative to the CTA's first byte
-    uint32_t len[COUNT_SLOTS];
+    uint32_t pos[COUNT_SLOTS];  // byte position of one occurrence, relative to the CTA's first byte (length: from the mask)
 };
 
 #define COUNT_SMEM (sizeof(SharedTable) + (COUNT_THREADS / 32) * 1056 * sizeof(unsigned short))
 
-__device__ __forceinline__ bool token_is_special(const Specials& sp, const uint8_t* __restrict__ text, uint64_t p, uint64_t len) {
-    uint8_t b0 = text[p];
-    if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return false;
+// fb = up to four distinct first bytes of the special tokens packed in a word (0xFF = unused), so that the common
+// "not a special token" answer costs a few register compares instead of an indexed read of the kernel parameters.
+__device__ __forceinline__ bool token_is_special(const Specials& sp, uint32_t fb, const uint8_t* __restrict__ text, uint64_t p, uint64_t len) {
+    const uint32_t b0 = text[p];
+    if (fb != 0xFFFFFFFEu) {
+        if (b0 != (fb & 0xFF) && b0 != ((fb >> 8) & 0xFF) && b0 != ((fb >> 16) & 0xFF) && b0 != (fb >> 24)) return false;
+    } else if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return false;
     for (int s = 0; s < sp.n; s++) {
         if (sp.off[s + 1] - sp.off[s] != len) continue;
         bool ok = true;
         for (uint32_t k = 0; k < len && ok; k++) ok = text[p + k] == sp.blob[sp.off[s] + k];
         if (ok) return true;
+    }
+    return false;
+}
+
+__device__ __forceinline__ uint32_t special_first_bytes(const Specials& sp) {
+    uint32_t fb = 0xFFFFFFFFu;
+    int used = 0;
+    for (int s = 0; s < sp.n; s++) {
+        uint32_t b = sp.blob[sp.off[s]];
+        bool seen = false;
+        for (int k = 0; k < used; k++) seen |= ((fb >> (8 * k)) & 0xFF) == b;
+        if (seen) continue;
+        if (used == 4 || b == 0xFF) return 0xFFFFFFFEu;  // too many / ambiguous: use the 256-bit set
+        fb = (fb & ~(0xFFu << (8 * used))) | (b << (8 * used));
+        used++;
+    }
+    return fb;
+}
+
+// Adds c to the count of an already-known key; false if the key is not in the table yet.
+__device__ __forceinline__ bool unique_bump(const UniqueTable& t, uint64_t key, uint64_t c) {
+    uint64_t slot = (key * 0xD6E8FEB86659FD93ull >> 17) & t.cap_mask;
+    for (int probe = 0; probe < 64; probe++) {
+        uint64_t cur = *reinterpret_cast<volatile uint64_t*>(t.key + slot);
+        if (cur == key) {
+            atomicAdd(reinterpret_cast<unsigned long long*>(t.cnt + slot), (unsigned long long)c);
+            return true;
+        }
+        if (cur == 0) return false;
+        slot = (slot + 1) & t.cap_mask;
     }
     return false;
 }
@@ -71,6 +104,7 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned short* pos = pos_all + warp * 1056;  // 1024 starts + 1 end marker, padded
     for (uint32_t k = threadIdx.x; k < COUNT_SLOTS; k += COUNT_THREADS) { st.key[k] = 0; st.cnt[k] = 0; }
+    const uint32_t fb = special_first_bytes(sp);
     __syncthreads();
 
     const uint64_t w_lo = (uint64_t)blockIdx.x * P.words_per_block;
@@ -103,10 +137,10 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
             const uint64_t p = kib + pos[t];
             const uint64_t e = (t + 1 < total) ? kib + pos[t + 1] : tail_end;
             const uint64_t len = e - p;
-            if (sp.n && token_is_special(sp, P.text, p, len)) continue;
+            if (sp.n && token_is_special(sp, fb, P.text, p, len)) continue;
             local_tokens++;
             bool done = false;
-            uint64_t key;
+            uint64_t key = 0;
             if (len < 0xFFFFFFFFull && p - base < 0xFFFFFFFFull) {
                 key = hash_key(P.text, p, (uint32_t)len);
                 uint32_t slot = (uint32_t)(key >> 40) & (COUNT_SLOTS - 1);
@@ -117,7 +151,6 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
                         cur = atomicCAS(&st.key[slot], 0ull, (unsigned long long)key);
                         if (cur == 0) {
                             st.pos[slot] = (uint32_t)(p - base);
-                            st.len[slot] = (uint32_t)len;
                             cur = key;
                         }
                     }
@@ -128,7 +161,8 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
                     slot = (slot + 1) & (COUNT_SLOTS - 1);
                 }
             }
-            if (!done) unique_insert(P.ut, P.status, P.text, p, (uint32_t)len, hash_bytes(P.text, p, len), 1);
+            // not in the shared table (full neighbourhood): bump the global entry; only a first sighting takes the slow path
+            if (!done && !(key && unique_bump(P.ut, key, 1))) unique_insert(P.ut, P.status, P.text, p, (uint32_t)len, hash_bytes(P.text, p, len), 1);
         }
         __syncwarp();
     }
@@ -137,7 +171,7 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
     for (uint32_t s = threadIdx.x; s < COUNT_SLOTS; s += COUNT_THREADS) {
         if (st.key[s] == 0) continue;
         uint64_t p = base + st.pos[s];
-        uint32_t len = st.len[s];
+        uint32_t len = (uint32_t)(token_end(P.start, P.n_words, p >> 5, __ldg(P.start + (p >> 5)), (uint32_t)(p & 31), P.n) - p);
         TokenKey k = hash_bytes(P.text, p, len);  // key again, plus the check word (not kept in shared memory)
         unique_insert(P.ut, P.status, P.text, p, len, k, st.cnt[s]);
     }

@@ -103,22 +103,13 @@ def count_shard(engine: "_lib.Engine", path, lo: int, hi: int, special_tokens: l
     engine.set_special_tokens(_lib.sort_specials(special_tokens))
     if reset:
         engine.unique_reset()
-    n = hi - lo
-    host = torch.empty(n, dtype=torch.uint8, pin_memory=True)
-    if n:
-        with open(path, "rb", buffering=0) as fh:
-            fh.seek(lo)
-            view, got = memoryview(host.numpy()), 0
-            while got < n:
-                k = fh.readinto(view[got:])
-                if not k:
-                    raise OSError(f"short read on {path}")
-                got += k
-    d_text, n = engine.to_device(host)
+    d_text, n = engine.load_file(path, lo, hi)
     try:
         mask = engine.scan(d_text, n)
     except _lib.InvalidUtf8:
-        clean, _ = _sanitised(bytes(memoryview(host.numpy())), [], strict=False)
+        with open(path, "rb") as fh:
+            fh.seek(lo)
+            clean, _ = _sanitised(fh.read(hi - lo), [], strict=False)
         d_text, n = engine.to_device(clean)
         mask = engine.scan(d_text, n)
     engine.count(d_text, n, mask)
@@ -154,14 +145,7 @@ def encode_file_sharded(tokenizer, path, group=None) -> tuple[np.ndarray, int, i
     engine = _lib.get_engine()
     offs = line_shard_offsets(path, world)
     lo, hi = offs[rank], offs[rank + 1]
-    host = torch.empty(hi - lo, dtype=torch.uint8, pin_memory=True)
-    if hi > lo:
-        with open(path, "rb", buffering=0) as fh:
-            fh.seek(lo)
-            view, got = memoryview(host.numpy()), 0
-            while got < hi - lo:
-                got += fh.readinto(view[got:])
-    ids = tokenizer._ids_to_numpy(tokenizer.encode_bytes_to_device(host, flags=_lib.CUT_AFTER_NEWLINE, engine=engine))
+    ids = tokenizer.encode_device_to_array(engine.load_file(path, lo, hi), engine)
     counts = [torch.zeros(1, dtype=torch.int64, device=f"cuda:{engine.device}") for _ in range(world)]
     dist.all_gather(counts, torch.tensor([len(ids)], dtype=torch.int64, device=f"cuda:{engine.device}"), group=group)
     counts = [int(c.item()) for c in counts]

@@ -208,14 +208,14 @@ class BPETokenizer(Tokenizer):
         """Array-returning sibling of encode_iterable(open(path)): the whole UTF-8 file -> numpy uint16 / uint32
         ids (the format a 1-D token dataset uses).  Files with '\\r' go through Python's universal-newline
         translation first, as open(path) would do."""
-        from .preprocessing.pretokenization import read_file_pinned
-
         engine = engine or _lib.get_engine()
-        host = read_file_pinned(path)
-        on_device = engine.to_device(host)
+        return self.encode_device_to_array(engine.load_file(path), engine, cut_after_newline)
+
+    def encode_device_to_array(self, on_device, engine: "_lib.Engine", cut_after_newline: bool = True) -> np.ndarray:
+        """(padded device text, length) -> NumPy ids, cutting after every newline like a file handle's line iteration."""
         d_text, n = on_device
         if n and bool((d_text[:n] == 13).any().item()):  # '\r': what text mode translates before the reference sees lines
-            data = bytes(memoryview(host.numpy())).replace(b"\r\n", b"\n").replace(b"\r", b"\n")
+            data = d_text[:n].cpu().numpy().tobytes().replace(b"\r\n", b"\n").replace(b"\r", b"\n")
             on_device = engine.to_device(data)
         ids = self.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE if cut_after_newline else 0, engine=engine, on_device=on_device)
-        return self._ids_to_numpy(ids)
+        return engine.to_host_array(ids, np.uint16 if ids.element_size() == 2 else np.uint32)

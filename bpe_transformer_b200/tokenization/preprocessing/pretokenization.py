@@ -120,7 +120,6 @@ def count_into_engine(engine: "_lib.Engine", file_path, special_tokens: list[str
     engine.set_special_tokens(specials)
     if reset:
         engine.unique_reset()
-    host = read_file_pinned(file_path)
     cuts: list[int] = []
     if not specials:
         # Without special tokens the reference cuts the file at newlines chosen by the worker count; a cut is a
@@ -128,11 +127,12 @@ def count_into_engine(engine: "_lib.Engine", file_path, special_tokens: list[str
         # starts, where a segment ends anyway.)
         with open(file_path, "rb") as fh:
             cuts = find_chunk_boundaries(fh, n_chunks, None)[1:-1]
-    d_text, n = engine.to_device(host)
+    d_text, n = engine.load_file(file_path)
     try:
         mask = engine.scan(d_text, n, cuts=cuts)
     except _lib.InvalidUtf8:
-        clean, cuts = _sanitised(bytes(memoryview(host.numpy())), cuts, strict)
+        with open(file_path, "rb") as fh:
+            clean, cuts = _sanitised(fh.read(), cuts, strict)
         d_text, n = engine.to_device(clean)
         mask = engine.scan(d_text, n, cuts=cuts)
     engine.count(d_text, n, mask)

@@ -62,6 +62,17 @@ int bpe_ctx_configure(bpe_ctx* ctx, int table_log2, uint64_t pool_bytes);
  * split_on_special_tokens does (pretokenization.py:228-232).  n = 0 clears them. */
 int bpe_set_special_tokens(bpe_ctx* ctx, const uint8_t* h_blob, const uint32_t* h_off, int n);
 
+/* ---- host I/O staging (the step before and after the path) ----------------------------------- */
+
+/* Reads bytes [offset, offset + n) of the file at `path` into the device buffer d_dst: several reader threads fill
+ * persistent pinned staging buffers while the previous chunk is copied to the GPU.  Replaces the f.seek / f.read of
+ * the reference's workers (pretokenization.py:192-194).  The copy has completed on return. */
+int bpe_load_file(bpe_ctx* ctx, const char* path, uint64_t offset, uint64_t n, uint8_t* d_dst, void* stream);
+
+/* Copies n bytes from device memory to an ordinary (pageable) host array through the same staging buffers, e.g. the
+ * ids of bpe_encode into a NumPy array — the 1-D token dataset format.  Waits for `stream` first. */
+int bpe_store_to_host(bpe_ctx* ctx, const void* d_src, uint64_t n, void* h_dst, void* stream);
+
 /* ---- pretokenisation ---------------------------------------------------------------------------------- */
 
 /* Token-start bitmask of d_text[0, n): bit (i & 31) of d_start[i >> 5] is set iff a token starts at byte i.

@@ -6,14 +6,13 @@ import torch
 import bench
 from bpe_transformer_b200 import _lib
 from bpe_transformer_b200.tokenization import BPETrainer
-from bpe_transformer_b200.tokenization.preprocessing.pretokenization import read_file_pinned
 
 nbytes = int(sys.argv[1]) if len(sys.argv) > 1 else 2_100_000_000
 path = bench.corpus_path(nbytes)
 bench.make_corpus(path, nbytes)
 eng = _lib.get_engine(0)
 eng.set_special_tokens(_lib.sort_specials([bench.EOT]))
-d_text, n = eng.to_device(read_file_pinned(path))
+d_text, n = eng.load_file(path)
 ref = None
 for ctas in sys.argv[2:] or ["0"]:
     if ctas == "0":
