@@ -103,7 +103,10 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
     unsigned short* pos_all = reinterpret_cast<unsigned short*>(smem_raw + sizeof(SharedTable));
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned short* pos = pos_all + warp * 1056;  // 1024 starts + 1 end marker, padded
+    __shared__ unsigned int sh_used_word;
+    unsigned int* sh_used = &sh_used_word;
     for (uint32_t k = threadIdx.x; k < COUNT_SLOTS; k += COUNT_THREADS) { st.key[k] = 0; st.cnt[k] = 0; }
+    if (threadIdx.x == 0) sh_used_word = 0;
     const uint32_t fb = special_first_bytes(sp);
     __syncthreads();
 
@@ -133,7 +136,10 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
         tail_end = __shfl_sync(0xFFFFFFFFu, tail_end, last_lane);
         __syncwarp();
         const uint64_t kib = w0 * 32;
-        for (uint32_t t = lane; t < total; t += 32) {
+        for (uint32_t t0 = 0; t0 < total; t0 += 32) {  // warp-uniform trip count: the lanes re-converge every round
+            __syncwarp();
+            const uint32_t t = t0 + lane;
+            if (t >= total) continue;
             const uint64_t p = kib + pos[t];
             const uint64_t e = (t + 1 < total) ? kib + pos[t + 1] : tail_end;
             const uint64_t len = e - p;
@@ -148,9 +154,13 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
                 for (int probe = 0; probe < COUNT_PROBES && !done; probe++) {
                     unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&st.key[slot]);
                     if (cur == 0) {
+                        // an empty slot ends the search.  New keys are admitted only while the table is at most half full:
+                        // a fuller table would make every lookup walk long probe chains (and the lanes of a warp diverge).
+                        if (*reinterpret_cast<volatile unsigned int*>(sh_used) >= COUNT_SLOTS / 2) break;
                         cur = atomicCAS(&st.key[slot], 0ull, (unsigned long long)key);
                         if (cur == 0) {
                             st.pos[slot] = (uint32_t)(p - base);
+                            atomicAdd(sh_used, 1u);
                             cur = key;
                         }
                     }
