@@ -13,7 +13,6 @@
 #include "common.cuh"
 
 #define SCAN_THREADS 256
-#define SCAN_HALO 2  // chunks in front of a tile that are searched for special tokens reaching into it
 
 namespace {
 
@@ -34,26 +33,6 @@ __device__ __forceinline__ uint32_t sw_range(uint32_t y, uint32_t lo, uint32_t h
 __device__ __forceinline__ uint32_t sw_eq(uint32_t y, uint32_t c) { return ~((y ^ (c * 0x01010101u)) + 0x7F7F7F7Fu); }
 // 0x80-per-byte flags -> 4-bit nibble (bit k = byte k)
 __device__ __forceinline__ uint32_t sw_collapse(uint32_t m) { return (((m >> 7) & 0x01010101u) * 0x00204081u >> 21) & 0xFu; }
-
-struct WordClass {
-    uint32_t L, N, S, SP, AP, NL, HI, FB;  // 0x80 flags (garbage in the low 7 bits of each byte until collapsed)
-};
-
-__device__ __forceinline__ WordClass classify_word(uint32_t w, uint32_t fb0, uint32_t fb1) {
-    WordClass c;
-    uint32_t hi = w & 0x80808080u;
-    uint32_t y = w & 0x7F7F7F7Fu;
-    uint32_t ascii = ~hi;
-    c.HI = hi;
-    c.L = sw_range(y | 0x20202020u, 'a', 'z') & ascii;
-    c.N = sw_range(y, '0', '9') & ascii;
-    c.SP = sw_eq(y, ' ') & ascii;
-    c.S = (sw_range(y, 9, 13) & ascii) | c.SP;
-    c.AP = sw_eq(y, '\'') & ascii;
-    c.NL = sw_eq(y, '\n') & ascii;
-    c.FB = (sw_eq(y, fb0) | sw_eq(y, fb1)) & ascii;
-    return c;
-}
 
 // ---- scalar helpers for the rare paths ------------------------------------------------------------------------
 // Strict UTF-8 decode of the character that contains byte `pos`.  Returns false if that byte is not part of
@@ -98,27 +77,6 @@ __device__ uint32_t class_containing(const ScanParams& P, uint64_t pos) {
     return cp_class(P.cls, cp);
 }
 
-struct Tile {
-    uint64_t byte0;        // first byte of the tile's core
-    const uint32_t* wall;  // shared: words for chunks [-SCAN_HALO, SCAN_THREADS + 1)
-};
-
-__device__ __forceinline__ bool wall_bit(const Tile& T, int64_t rel) {  // rel = byte position relative to the tile core
-    int64_t idx = rel + SCAN_HALO * 32;
-    return (T.wall[idx >> 5] >> (idx & 31)) & 1u;
-}
-
-// Is there a segment boundary directly in front of byte `pos`?  (text start / end, after a special token,
-// before a special token, at a caller cut, after a newline in newline mode)
-__device__ bool boundary_before(const ScanParams& P, const Tile& T, uint64_t pos) {
-    if (pos == 0 || pos >= P.n) return true;
-    int64_t rel = (int64_t)pos - (int64_t)T.byte0;
-    if (wall_bit(T, rel) || wall_bit(T, rel - 1)) return true;
-    if (P.cutmask && ((P.cutmask[pos >> 5] >> (pos & 31)) & 1u)) return true;
-    if ((P.flags & BPE_CUT_AFTER_NEWLINE) && P.text[pos - 1] == '\n') return true;
-    return false;
-}
-
 // First position > p at which a special token starting at p must end at the latest: the next cut.
 __device__ uint64_t piece_limit(const ScanParams& P, uint64_t p, int max_len) {
     uint64_t lim = p + (uint64_t)max_len < P.n ? p + (uint64_t)max_len : P.n;
@@ -156,18 +114,20 @@ __device__ bool special_is_real(const ScanParams& P, const Specials& sp, uint64_
     return pos == p;
 }
 
-__device__ void mark_special(const ScanParams& P, const Specials& sp, uint64_t tile0, uint32_t* wall, uint32_t* sps, uint64_t p) {
-    uint32_t L = special_len_at(P, sp, p);
-    if (!L || !special_is_real(P, sp, p)) return;
-    int64_t rel = (int64_t)p - (int64_t)tile0 + SCAN_HALO * 32;
-    int64_t hi = (int64_t)(SCAN_THREADS + SCAN_HALO + 1) * 32;
-    atomicOr(&sps[rel >> 5], 1u << (rel & 31));
-    for (int64_t q = rel; q < rel + (int64_t)L && q < hi; q++) atomicOr(&wall[q >> 5], 1u << (q & 31));
-}
+#define SCAN_LG 2                                    // ghost chunks in front of a tile's core (special tokens up to 60 bytes reach in)
+#define SCAN_RG 1                                    // ghost chunk behind it
+#define SCAN_CORE (SCAN_THREADS - SCAN_LG - SCAN_RG)  // chunks of 32 bytes a tile produces
 
+// A tile is SCAN_THREADS chunks of 32 bytes, one per thread; the first two and the last one are ghosts: they are
+// classified like the others (so that their neighbours can read the classes next to their own bytes from shared
+// memory instead of classifying extra words) but their result belongs to the neighbouring tile.
+template <bool NLMODE>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const ScanParams P, const __grid_constant__ Specials sp) {
-    __shared__ uint32_t wall[SCAN_THREADS + SCAN_HALO + 1];  // bytes covered by a special token
-    __shared__ uint32_t sps[SCAN_THREADS + SCAN_HALO + 1];   // first byte of a special token
+    __shared__ uint32_t wall[SCAN_THREADS + 2];  // bytes covered by a special token, per chunk of the tile
+    __shared__ uint32_t sps[SCAN_THREADS + 2];   // first byte of a special token
+    __shared__ uint32_t e_hi[SCAN_THREADS];      // classes of a chunk's last four bytes: 4 bits each of L, N, S, SP, NL, RARE
+    __shared__ uint32_t e_lo[SCAN_THREADS];      // ... of its first four bytes
+    __shared__ uint32_t fbm[SCAN_THREADS];       // bytes that can begin a special token
     const uint32_t tid = threadIdx.x;
     const uint32_t fb0 = sp.n ? sp.blob[sp.off[0]] : 0xFFu;  // up to two distinct ASCII first bytes go the fast way
     uint32_t fb1 = fb0;
@@ -178,159 +138,161 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const ScanParams P, 
         else if (b != fb0 && fb1 == fb0) fb1 = b;
         else if (b != fb0 && b != fb1) fb_generic = true;
     }
-    const bool nlmode = P.flags & BPE_CUT_AFTER_NEWLINE;
 
     for (uint64_t tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-        const uint64_t tile0 = tile * (uint64_t)(SCAN_THREADS * 32);
-        const uint64_t c0 = tile0 + (uint64_t)tid * 32;  // first byte of this thread's chunk
-        for (uint32_t k = tid; k < SCAN_THREADS + SCAN_HALO + 1; k += SCAN_THREADS) { wall[k] = 0; sps[k] = 0; }
+        const int64_t chunk = (int64_t)tile * SCAN_CORE - SCAN_LG + tid;  // may lie in front of the text (first tile)
+        const bool exists = chunk >= 0 && (uint64_t)chunk * 32 < P.n;
+        const uint64_t c0 = exists ? (uint64_t)chunk * 32 : 0;
+        const uint32_t valid = !exists ? 0u : (P.n - c0 >= 32 ? 0xFFFFFFFFu : ((1u << (uint32_t)(P.n - c0)) - 1u));
+        wall[tid] = 0; sps[tid] = 0;
+        if (tid < 2) { wall[SCAN_THREADS + tid] = 0; sps[SCAN_THREADS + tid] = 0; }
 
-        // ---- load 32 bytes + 4 before + 4 after, classify ------------------------------------------------
-        uint32_t w[10];
-        {
+        // ---- phase A: 32 bytes -> class masks -------------------------------------------------------------------
+        uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (exists) {
             const uint4* q = reinterpret_cast<const uint4*>(P.text + c0);
-            uint4 a = make_uint4(0, 0, 0, 0), b = a;
-            if (c0 < P.n) a = __ldg(q);
+            uint4 a = __ldg(q), b = make_uint4(0, 0, 0, 0);
             if (c0 + 16 < P.n) b = __ldg(q + 1);
-            w[1] = a.x; w[2] = a.y; w[3] = a.z; w[4] = a.w; w[5] = b.x; w[6] = b.y; w[7] = b.z; w[8] = b.w;
-            w[0] = (c0 >= 4 && c0 - 4 < P.n) ? __ldg(reinterpret_cast<const uint32_t*>(P.text + c0 - 4)) : 0u;
-            w[9] = (c0 + 32 < P.n) ? __ldg(reinterpret_cast<const uint32_t*>(P.text + c0 + 32)) : 0u;
+            w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
         }
-        uint32_t L = 0, N = 0, S = 0, SP = 0, AP = 0, NL = 0, HI = 0, FB = 0;
+        uint32_t L = 0, N = 0, S = 0, SP = 0, NL = 0, RARE = 0, FB = 0;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            WordClass c = classify_word(w[k + 1], fb0, fb1);
-            L |= sw_collapse(c.L) << (4 * k);
-            N |= sw_collapse(c.N) << (4 * k);
-            S |= sw_collapse(c.S) << (4 * k);
-            SP |= sw_collapse(c.SP) << (4 * k);
-            AP |= sw_collapse(c.AP) << (4 * k);
-            NL |= sw_collapse(c.NL) << (4 * k);
-            HI |= sw_collapse(c.HI) << (4 * k);
-            FB |= sw_collapse(c.FB) << (4 * k);
+            const uint32_t hi = w[k] & 0x80808080u, y = w[k] & 0x7F7F7F7Fu, ascii = ~hi;
+            const uint32_t cL = sw_range(y | 0x20202020u, 'a', 'z') & ascii;
+            const uint32_t cN = sw_range(y, '0', '9') & ascii;
+            const uint32_t cSP = sw_eq(y, ' ') & ascii;
+            const uint32_t cS = (sw_range(y, 9, 13) & ascii) | cSP;
+            const uint32_t cRare = (sw_eq(y, '\'') & ascii) | hi;  // apostrophes and non-ASCII bytes: handled one by one
+            L |= sw_collapse(cL) << (4 * k);
+            N |= sw_collapse(cN) << (4 * k);
+            S |= sw_collapse(cS) << (4 * k);
+            SP |= sw_collapse(cSP) << (4 * k);
+            RARE |= sw_collapse(cRare) << (4 * k);
+            if (NLMODE) NL |= sw_collapse(sw_eq(y, '\n') & ascii) << (4 * k);
+            if (sp.n) FB |= sw_collapse((sw_eq(y, fb0) | sw_eq(y, fb1)) & ascii) << (4 * k);
         }
-        WordClass cp_ = classify_word(w[0], fb0, fb1), cn_ = classify_word(w[9], fb0, fb1);
-        // previous four bytes in bits 28..31, next four bytes in bits 0..3
-        uint32_t Lp = sw_collapse(cp_.L) << 28, Np = sw_collapse(cp_.N) << 28, Sp = sw_collapse(cp_.S) << 28, SPp = sw_collapse(cp_.SP) << 28;
-        uint32_t APp = sw_collapse(cp_.AP) << 28, NLp = sw_collapse(cp_.NL) << 28, HIp = sw_collapse(cp_.HI) << 28;
-        uint32_t Ln = sw_collapse(cn_.L), Nn = sw_collapse(cn_.N), Sn = sw_collapse(cn_.S), HIn = sw_collapse(cn_.HI);
-
-        // bytes at or beyond n do not exist
-        uint32_t valid = (c0 >= P.n) ? 0u : (P.n - c0 >= 32 ? 0xFFFFFFFFu : ((1u << (uint32_t)(P.n - c0)) - 1u));
-        uint32_t validn = (c0 + 32 >= P.n) ? 0u : (P.n - c0 - 32 >= 4 ? 0xFu : ((1u << (uint32_t)(P.n - c0 - 32)) - 1u));
+        L &= valid; N &= valid; S &= valid; SP &= valid; RARE &= valid; NL &= valid;
         if (fb_generic) {
             FB = 0;
             for (uint32_t b = 0; b < 32; b++) {
-                uint32_t x = (w[1 + (b >> 2)] >> (8 * (b & 3))) & 0xFF;
+                uint32_t x = (w[b >> 2] >> (8 * (b & 3))) & 0xFF;
                 if ((sp.first_byte_mask[x >> 5] >> (x & 31)) & 1u) FB |= 1u << b;
             }
         }
         FB &= valid;
-        __syncthreads();  // wall / sps cleared
+        // rare bytes one by one: non-ASCII (decode, class table, strict validation) and apostrophes
+        uint32_t AP = 0, CONT = 0, HI = 0;
+        for (uint32_t m = RARE; m; m &= m - 1) {
+            const uint32_t b = __ffs(m) - 1;
+            const uint32_t byte = (w[b >> 2] >> (8 * (b & 3))) & 0xFF;
+            if (byte == '\'') { AP |= 1u << b; continue; }
+            HI |= 1u << b;
+            uint64_t lead; uint32_t len, cp;
+            if (!char_containing(P.text, c0 + b, P.n, &lead, &len, &cp)) { set_status(P.status, ST_INVALID_UTF8); continue; }
+            const uint32_t k = cp_class(P.cls, cp);
+            if (k == CLS_L) L |= 1u << b; else if (k == CLS_N) N |= 1u << b; else if (k == CLS_S) S |= 1u << b;
+            if (lead != c0 + b) CONT |= 1u << b;
+        }
+        e_hi[tid] = (L >> 28) | ((N >> 28) << 4) | ((S >> 28) << 8) | ((SP >> 28) << 12) | ((NL >> 28) << 16) | ((AP >> 28) << 20);
+        e_lo[tid] = (L & 15u) | ((N & 15u) << 4) | ((S & 15u) << 8) | ((SP & 15u) << 12) | ((NL & 15u) << 16) | ((AP & 15u) << 20);
+        fbm[tid] = FB;
+        __syncthreads();
 
-        // ---- phase 1: special tokens that start in this chunk (or, for a few threads, in the halo chunks) ----
+        // ---- phase B: special tokens that start in this chunk ---------------------------------------------------------
         if (sp.n) {
-            for (uint32_t m = FB; m; m &= m - 1) mark_special(P, sp, tile0, wall, sps, c0 + (__ffs(m) - 1));
-            if (tid <= SCAN_HALO) {
-                int64_t chunk = (tid < SCAN_HALO) ? -(int64_t)(tid + 1) : (int64_t)SCAN_THREADS;
-                int64_t b0 = (int64_t)tile0 + chunk * 32;
-                for (int64_t p = b0; p < b0 + 32; p++)
-                    if (p >= 0 && (uint64_t)p < P.n) {
-                        uint8_t x = P.text[p];
-                        if ((sp.first_byte_mask[x >> 5] >> (x & 31)) & 1u) mark_special(P, sp, tile0, wall, sps, (uint64_t)p);
-                    }
+            for (uint32_t m = FB; m; m &= m - 1) {
+                const uint32_t b = __ffs(m) - 1;
+                const uint64_t p = c0 + b;
+                const uint32_t len = special_len_at(P, sp, p);
+                if (!len) continue;
+                // another candidate within max_len - 1 bytes in front of p could cover it: then replay the scan exactly
+                bool lonely = false;
+                if (tid >= 2) {
+                    const uint64_t before = ((uint64_t)fbm[tid - 2]) | ((uint64_t)fbm[tid - 1] << 32);  // 64 bytes in front of the chunk
+                    const uint64_t own = FB & ((1u << b) - 1u);
+                    // bits of the 96-byte window [c0 - 64, c0 + 32) that lie in [p - (max_len - 1), p)
+                    const uint32_t reach = (uint32_t)sp.max_len - 1;  // <= 59
+                    uint64_t near_prev = reach > b ? before >> (64 - (reach - b)) : 0;  // the top (reach - b) bits
+                    uint64_t near_own = reach >= b ? own : own >> (b - reach);
+                    lonely = !(near_prev | near_own);
+                }
+                if (!lonely && !special_is_real(P, sp, p)) continue;
+                atomicOr(&sps[tid], 1u << b);
+                const uint64_t bits = ((1ull << len) - 1ull);  // len <= 60: spans at most three chunks
+                const uint64_t lo64 = bits << b;
+                atomicOr(&wall[tid], (uint32_t)lo64);
+                if (b + len > 32) atomicOr(&wall[tid + 1], (uint32_t)(lo64 >> 32));
+                if (b + len > 64) atomicOr(&wall[tid + 2], (uint32_t)(bits >> (64 - b)));
             }
         }
         __syncthreads();
 
-        if (c0 < P.n) {
-            Tile T{tile0, wall};
-            uint32_t W = wall[tid + SCAN_HALO] | ~valid;
-            uint32_t Wp = (c0 == 0) ? 0xFFFFFFFFu : wall[tid + SCAN_HALO - 1];
-            uint32_t Wn = wall[tid + SCAN_HALO + 1] | ~validn;
-            uint32_t SPS = sps[tid + SCAN_HALO];
-            uint32_t CONT = 0;
-
-            // ---- non-ASCII: decode, look the class up, validate ---------------------------------------------
-            if ((HI & valid) | HIp | (HIn & validn)) {
-                for (uint32_t m = HI & valid; m; m &= m - 1) {
-                    uint32_t b = __ffs(m) - 1;
-                    uint64_t lead; uint32_t len, cp;
-                    if (!char_containing(P.text, c0 + b, P.n, &lead, &len, &cp)) { set_status(P.status, ST_INVALID_UTF8); continue; }
-                    uint32_t k = cp_class(P.cls, cp);
-                    if (k == CLS_L) L |= 1u << b; else if (k == CLS_N) N |= 1u << b; else if (k == CLS_S) S |= 1u << b;
-                    if (lead != c0 + b) CONT |= 1u << b;
-                }
-                if (HIp >> 31) {  // only the class of the byte right in front matters to the bit-parallel rule
-                    uint32_t k = class_containing(P, c0 - 1);
-                    if (k == CLS_L) Lp |= 1u << 31; else if (k == CLS_N) Np |= 1u << 31; else if (k == CLS_S) Sp |= 1u << 31;
-                }
-                if (HIn & validn & 1u) {
-                    uint32_t k = class_containing(P, c0 + 32);
-                    if (k == CLS_L) Ln |= 1u; else if (k == CLS_N) Nn |= 1u; else if (k == CLS_S) Sn |= 1u;
-                }
+        // ---- phase C: the split pattern, 32 bytes at a time -------------------------------------------------------------------
+        if (exists && tid >= SCAN_LG && tid < SCAN_THREADS - SCAN_RG) {
+            const bool first = chunk == 0;
+            const uint32_t ph = first ? 0u : e_hi[tid - 1], nl = e_lo[tid + 1];
+            const uint32_t W = wall[tid] | ~valid;
+            const uint32_t Wp = first ? 0xFFFFFFFFu : wall[tid - 1];
+            const uint64_t n_next = (uint64_t)(chunk + 1) * 32;
+            const uint32_t validn = n_next >= P.n ? 0u : (P.n - n_next >= 32 ? 0xFFFFFFFFu : ((1u << (uint32_t)(P.n - n_next)) - 1u));
+            const uint32_t Wn = wall[tid + 1] | ~validn;
+            L &= ~W; N &= ~W; S &= ~W; SP &= ~W; AP &= ~W;
+            // 40-bit views: bit 0..3 = the four bytes in front of the chunk, 4..35 = the chunk, 36..39 = the four behind it
+            auto wide = [](uint32_t prev4, uint32_t core, uint32_t next4) { return (uint64_t)prev4 | ((uint64_t)core << 4) | ((uint64_t)next4 << 36); };
+            const uint64_t W64 = wide(Wp >> 28, W, Wn & 15u);
+            const uint64_t L64 = wide(ph & 15u, L, nl & 15u) & ~W64, N64 = wide((ph >> 4) & 15u, N, (nl >> 4) & 15u) & ~W64;
+            const uint64_t S64 = wide((ph >> 8) & 15u, S, (nl >> 8) & 15u) & ~W64, SP64 = wide((ph >> 12) & 15u, SP, (nl >> 12) & 15u) & ~W64;
+            uint64_t PN64 = (W64 << 1) | W64;  // bit j: a segment boundary between bytes j - 1 and j (a wall on either side, a cut)
+            if (first) PN64 |= 0x1Full;
+            if (P.cutmask) {
+                const uint32_t cut = __ldg(P.cutmask + (c0 >> 5)), cutp = first ? 0u : __ldg(P.cutmask + (c0 >> 5) - 1), cutn = __ldg(P.cutmask + (c0 >> 5) + 1);
+                PN64 |= wide(cutp >> 28, cut, cutn & 15u);
             }
-
-            // ---- the rule, 32 bytes at a time ------------------------------------------------------------------
-            uint32_t cut = P.cutmask ? __ldg(P.cutmask + (c0 >> 5)) : 0u;
-            uint32_t cutn = P.cutmask ? __ldg(P.cutmask + (c0 >> 5) + 1) : 0u;
-            uint32_t PN = ((W << 1) | (Wp >> 31)) | cut;                  // nothing in front of this byte in its segment
-            uint32_t NN = ((W >> 1) | (Wn << 31)) | ((cut >> 1) | (cutn << 31));  // nothing behind it
-            if (nlmode) { PN |= (NL << 1) | (NLp >> 31); NN |= NL; }
-            L &= ~W; N &= ~W; S &= ~W; SP &= ~W;
-            uint32_t O = ~(L | N | S | W);
-            uint32_t pL = (L << 1) | (Lp >> 31), pN = (N << 1) | (Np >> 31), pS = (S << 1) | (Sp >> 31), pSP = (SP << 1) | (SPp >> 31);
-            uint32_t pO = ~(pL | pN | pS);  // only read where the previous byte exists and is no wall
-            uint32_t nonS = L | N | O;
-            uint32_t nNonS = ((nonS >> 1) | ((~Sn & 1u) << 31)) & ~NN;   // the next byte exists and is not whitespace
-            uint32_t diff = (L & ~pL) | (N & ~pN) | (O & ~pO);
-            uint32_t startNS = nonS & (PN | (~pSP & (pS | diff)));
-            uint32_t startS = S & (PN | ~pS | nNonS);
+            if (NLMODE) PN64 |= wide((ph >> 16) & 15u, NL, (nl >> 16) & 15u) << 1;
+            const uint32_t PN = (uint32_t)(PN64 >> 4), NN = (uint32_t)(PN64 >> 5);
+            const uint32_t pL = (uint32_t)(L64 >> 3), pN = (uint32_t)(N64 >> 3), pS = (uint32_t)(S64 >> 3), pSP = (uint32_t)(SP64 >> 3);
+            const uint32_t O = ~(L | N | S | W);
+            const uint32_t pO = ~(pL | pN | pS);  // only read where the previous byte exists and is no wall
+            const uint32_t nonS = L | N | O;
+            const uint32_t nNonS = ~(uint32_t)(S64 >> 5) & ~NN;  // the next byte exists and is not whitespace
+            const uint32_t diff = (L & ~pL) | (N & ~pN) | (O & ~pO);
+            const uint32_t startNS = nonS & (PN | (~pSP & (pS | diff)));
+            const uint32_t startS = S & (PN | ~pS | nNonS);
             uint32_t start = (startNS | startS) & ~CONT;
 
             // multi-byte whitespace (NBSP, U+2000.., U+3000): "followed by non-whitespace" looks past the whole character
             for (uint32_t m = S & HI & ~CONT & ~start; m; m &= m - 1) {
-                uint32_t b = __ffs(m) - 1;
+                const uint32_t b = __ffs(m) - 1;
                 uint64_t lead; uint32_t len, cp;
                 if (!char_containing(P.text, c0 + b, P.n, &lead, &len, &cp)) continue;
-                uint64_t nx = c0 + b + len;
-                if (!boundary_before(P, T, nx) && class_containing(P, nx) != CLS_S) start |= 1u << b;
+                const uint32_t nx = b + len + 4;  // 40-bit index of the next character
+                if (!((PN64 >> nx) & 1u) && c0 + b + len < P.n && class_containing(P, c0 + b + len) != CLS_S) start |= 1u << b;
             }
 
-            // ---- contractions: an apostrophe that starts a token swallows s d m t / ll ve re --------------------------
-            uint32_t apc = AP & ~W;
-            uint64_t aph = APp >> 29;  // apostrophes 3, 2, 1 bytes in front of the chunk -> bits 0..2
-            if (apc | (uint32_t)aph) {
-                uint64_t cand = ((uint64_t)apc << 3) | aph;  // bit k <-> byte c0 + k - 3
-                for (; cand; cand &= cand - 1) {
-                    int64_t a = (int64_t)c0 + (__ffsll((long long)cand) - 1) - 3;
-                    if (a < 0 || (uint64_t)a >= P.n) continue;
-                    uint64_t ua = (uint64_t)a;
-                    if (wall_bit(T, a - (int64_t)tile0)) continue;
-                    bool starts = boundary_before(P, T, ua);
-                    if (!starts) {
-                        uint32_t pb = P.text[ua - 1];
-                        uint32_t k = class_containing(P, ua - 1);
-                        starts = (k == CLS_L) || (k == CLS_N) || (k == CLS_S && pb != ' ');
-                    }
-                    if (!starts || boundary_before(P, T, ua + 1)) continue;
-                    uint32_t b1 = P.text[ua + 1];
-                    uint64_t after = 0;  // first byte behind the contraction
-                    if (b1 == 's' || b1 == 'd' || b1 == 'm' || b1 == 't') after = ua + 2;
-                    else if (!boundary_before(P, T, ua + 2)) {
-                        uint32_t b2 = P.text[ua + 2];
-                        if ((b1 == 'l' && b2 == 'l') || (b1 == 'v' && b2 == 'e') || (b1 == 'r' && b2 == 'e')) after = ua + 3;
-                    }
-                    if (!after) continue;
-                    if (ua + 1 >= c0 && ua + 1 < c0 + 32) start &= ~(1u << (uint32_t)(ua + 1 - c0));  // the letter belongs to the apostrophe
-                    if (after >= c0 && after < c0 + 32 && !boundary_before(P, T, after) && class_containing(P, after) == CLS_L)
-                        start |= 1u << (uint32_t)(after - c0);  // a letter run begins behind the contraction
+            // contractions: an apostrophe that starts a token swallows s d m t / ll ve re
+            uint64_t AP64 = (uint64_t)AP << 4;
+            for (uint32_t m = (ph >> 20) & 14u; m; m &= m - 1) AP64 |= 1ull << (__ffs(m) - 1);  // apostrophes 3, 2, 1 bytes in front
+            AP64 &= ~W64;
+            for (; AP64; AP64 &= AP64 - 1) {
+                const uint32_t a = __ffsll((long long)AP64) - 1;  // 1 .. 35
+                const bool starts = ((PN64 >> a) & 1u) || (((L64 | N64 | (S64 & ~SP64)) >> (a - 1)) & 1u);
+                if (!starts || ((PN64 >> (a + 1)) & 1u)) continue;
+                const uint64_t pos = c0 + a - 4;  // byte position of the apostrophe
+                const uint32_t b1 = P.text[pos + 1];
+                uint32_t after = 0;  // 40-bit index of the first byte behind the contraction
+                if (b1 == 's' || b1 == 'd' || b1 == 'm' || b1 == 't') after = a + 2;
+                else if (!((PN64 >> (a + 2)) & 1u)) {
+                    const uint32_t b2 = P.text[pos + 2];
+                    if ((b1 == 'l' && b2 == 'l') || (b1 == 'v' && b2 == 'e') || (b1 == 'r' && b2 == 'e')) after = a + 3;
                 }
+                if (!after) continue;
+                if (a + 1 >= 4 && a + 1 < 36) start &= ~(1u << (a + 1 - 4));  // the letter belongs to the apostrophe
+                if (after >= 4 && after < 36 && !((PN64 >> after) & 1u) && ((L64 >> after) & 1u)) start |= 1u << (after - 4);
             }
-            start = (start & ~W) | SPS;
-            P.start[c0 >> 5] = start;
+            P.start[c0 >> 5] = (start & ~W) | sps[tid];
         }
-        __syncthreads();  // wall / sps are re-cleared by the next iteration
+        __syncthreads();  // shared arrays are rewritten by the next tile
     }
 }
 
@@ -345,16 +307,15 @@ __global__ void cuts_to_mask_kernel(const uint64_t* __restrict__ cuts, uint64_t 
 }  // namespace
 
 int launch_scan(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_cutmask, uint32_t flags, uint32_t* d_start, cudaStream_t s) {
-    uint64_t n_words = n / 32 + 2;
     CUDA_TRY(ctx, cudaMemsetAsync(d_start + (n / 32), 0, 2 * sizeof(uint32_t), s));
-    (void)n_words;
     if (n == 0) return BPE_OK;
     ScanParams P;
     P.text = d_text; P.n = n; P.cutmask = d_cutmask; P.flags = flags; P.start = d_start; P.status = ctx->d_status; P.cls = ctx->cls;
-    P.n_tiles = (n + SCAN_THREADS * 32 - 1) / (SCAN_THREADS * 32);
+    P.n_tiles = (n + SCAN_CORE * 32 - 1) / (SCAN_CORE * 32);
     uint64_t grid = P.n_tiles < (uint64_t)BPE_N_SM * 8 ? P.n_tiles : (uint64_t)BPE_N_SM * 8;
     KernelTimer t(ctx, "scan_kernel", s);
-    scan_kernel<<<(unsigned)grid, SCAN_THREADS, 0, s>>>(P, ctx->sp);
+    if (flags & BPE_CUT_AFTER_NEWLINE) scan_kernel<true><<<(unsigned)grid, SCAN_THREADS, 0, s>>>(P, ctx->sp);
+    else scan_kernel<false><<<(unsigned)grid, SCAN_THREADS, 0, s>>>(P, ctx->sp);
     CUDA_TRY(ctx, cudaGetLastError());
     return BPE_OK;
 }

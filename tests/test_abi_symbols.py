@@ -51,3 +51,18 @@ def test_product_does_not_import_the_oracle():
         src = path.read_text()
         assert "oracle" not in src.replace("the oracle compares", ""), f"{path} mentions the oracle"
         assert "import regex" not in src and "from regex" not in src, f"{path} imports regex"
+
+
+def test_gpt2_text_formats_round_trip(tmp_path):
+    """Host-only: formats.save_gpt2_files / load_gpt2_files against the golden GPT-2 model."""
+    from conftest import load_golden
+    from bpe_transformer_b200 import formats
+
+    g = load_golden("gpt2_model.json.gz")
+    vocab = {i: bytes.fromhex(h) for i, h in enumerate(g["vocab"])}
+    merges = [(bytes.fromhex(a), bytes.fromhex(b)) for a, b in g["merges"]]
+    formats.save_gpt2_files(vocab, merges, tmp_path / "v.json", tmp_path / "m.txt")
+    v2, m2 = formats.load_gpt2_files(tmp_path / "v.json", tmp_path / "m.txt")
+    assert v2 == vocab and m2 == merges
+    v3, _ = formats.load_gpt2_files(tmp_path / "v.json", tmp_path / "m.txt", ["<|new|>"])
+    assert v3[len(vocab)] == b"<|new|>"

@@ -337,6 +337,24 @@ def test_encode_error_conventions(gpt2_model):
     assert get_tokenizer(dict(vocab), merges, None).decode([0, 10**9, 1]) == port.PortTokenizer(vocab, merges).decode([0, 10**9, 1])
 
 
+def test_model_and_dataset_formats(tmp_path, gpt2_model, input_bytes, tmp_file):
+    """GPT-2 text formats round trip; a tokenized file lands in a .npy that holds encode_iterable's ids."""
+    from adapters import get_tokenizer
+    from bpe_transformer_b200 import formats
+
+    vocab, merges = gpt2_model
+    formats.save_gpt2_files(vocab, merges, tmp_path / "vocab.json", tmp_path / "merges.txt")
+    v2, m2 = formats.load_gpt2_files(tmp_path / "vocab.json", tmp_path / "merges.txt", [EOT])
+    assert m2 == merges and v2 == with_specials(vocab, [EOT])
+    tok = get_tokenizer(v2, m2, [EOT])
+    path = tmp_file(input_bytes("tinystories_sample.txt"))
+    ids = formats.encode_file_to_npy(tok, path, tmp_path / "ids.npy")
+    with open(path) as fh:
+        want = list(tok.encode_iterable(fh))
+    back = formats.load_token_dataset(tmp_path / "ids.npy")
+    assert back.dtype == np.uint16 and back.tolist() == want == ids.tolist()
+
+
 def test_large_roundtrip_and_conservation(tmp_path, ts10k_model):
     """Size-independent properties on a larger corpus (256 MB): occurrences == start bits outside specials,
     decode(encode(x)) == x through the GPU decoder, ids below the vocab size."""
