@@ -43,6 +43,7 @@ namespace cg = cooperative_groups;
 #define LIGHT_MAX 2048u         // posting lists up to this length are handled by the driver CTA alone
 #define QUEUE_CAP 2048u
 #define NONE 0xFFFFFFFFu
+#define MAX_TIES 1024u            // pairs that tie at the top count and are ordered by their bytes
 
 namespace {
 
@@ -231,6 +232,7 @@ __global__ void pairs_init_kernel(TrainState S, uint32_t n_words) {
 // 8-byte big-endian zero-padded prefixes order two byte strings whenever they differ; equal prefixes fall back to the
 // bytes (a shorter string that is a prefix of a longer one pads with 0x00 <= any byte, so "prefixes differ" is decisive).
 __device__ int token_cmp(const TrainState& S, uint32_t t, uint32_t u) {
+    if (S.flags & 4u) atomicAdd(&S.ctrl->dbg[6], 1u);  // experiments: how often ties in count reach the byte comparison
     if (t == u) return 0;
     unsigned long long pt = __ldcg(S.tk_pre + t), pu = __ldcg(S.tk_pre + u);
     if (pt != pu) return pt < pu ? -1 : 1;
@@ -398,8 +400,11 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
     };
     extern __shared__ __align__(16) unsigned char smem_raw[];
     HotCache& H = *reinterpret_cast<HotCache*>(smem_raw);  // used by the driver CTA only
-    __shared__ Best sh_best[NT / 32];
+    __shared__ long long sh_wmax[NT / 32];
+    __shared__ uint32_t sh_tie[MAX_TIES];
+    __shared__ unsigned int sh_ntie;
     __shared__ Best sh_win;
+    __shared__ Best sh_bestw[NT / 32];
     __shared__ uint32_t sh_queue[QUEUE_CAP];
     __shared__ unsigned int sh_qn;
     __shared__ unsigned int sh_hist[64];
@@ -532,41 +537,75 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             __syncthreads();
         }
         // ---- argmax over the cached pairs of (count, bytes(a), bytes(b)): shared memory only -------------------------------
+        // Two steps, so that byte strings are compared only for pairs that really tie at the top count (comparing
+        // them inside the reduction would chase token bytes through global memory for every tie among also-rans):
+        // (1) the maximum count, (2) the entries that have it — almost always exactly one.
         long long c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0;
         if (tracer) c0 = clock64();
         const uint32_t n_cached = use_cache ? H.n : 0;
         if (n_cached > HC) { need_rebuild = true; continue; }  // overflowed: compact (holes, leftovers) or raise T
-        Best best{0, 0, 0};
+        const uint32_t n_scan = use_cache ? n_cached : __ldcg(&S.ctrl->n_live);
+        long long my_max = 0;
         if (use_cache) {
-            for (uint32_t i = tid; i < n_cached; i += NT) {
-                Best c{H.cnt[i], H.key[i], i};
-                if (c.key && c.cnt > 0 && better(S, c, best)) best = c;
-            }
+            for (uint32_t i = tid; i < n_scan; i += NT) if (H.key[i]) my_max = max(my_max, H.cnt[i]);
         } else {
-            const uint32_t n_all = __ldcg(&S.ctrl->n_live);
-            for (uint32_t i = tid; i < n_all; i += NT) {
-                const uint32_t slot = __ldcg(S.live + i);
-                const long long cnt = __ldcg(S.ph_cnt + slot);
-                if (cnt <= 0 || cnt < best.cnt) continue;
-                Best c{cnt, __ldcg(S.ph_key + slot), slot};
-                if (better(S, c, best)) best = c;
+            for (uint32_t i = tid; i < n_scan; i += NT) my_max = max(my_max, __ldcg(S.ph_cnt + __ldcg(S.live + i)));
+        }
+        for (int o = 16; o; o >>= 1) my_max = max(my_max, __shfl_xor_sync(0xFFFFFFFFu, my_max, o));
+        if (lane == 0) sh_wmax[warp] = my_max;
+        if (tid == 0) sh_ntie = 0;
+        __syncthreads();
+        long long top = lane < NT / 32 ? sh_wmax[lane] : 0;  // every warp folds the per-warp maxima itself: no second barrier
+        for (int o = 16; o; o >>= 1) top = max(top, __shfl_xor_sync(0xFFFFFFFFu, top, o));
+        if (top > 0) {
+            if (use_cache) {
+                for (uint32_t i = tid; i < n_scan; i += NT)
+                    if (H.key[i] && H.cnt[i] == top) { uint32_t k = atomicAdd(&sh_ntie, 1u); if (k < MAX_TIES) sh_tie[k] = i; }
+            } else {
+                for (uint32_t i = tid; i < n_scan; i += NT) {
+                    const uint32_t slot = __ldcg(S.live + i);
+                    if (__ldcg(S.ph_cnt + slot) == top) { uint32_t k = atomicAdd(&sh_ntie, 1u); if (k < MAX_TIES) sh_tie[k] = slot; }
+                }
             }
         }
-        long long c0a = 0, c0b = 0, c0c = 0;
-        if (tracer) c0a = clock64();
-        for (int o = 16; o; o >>= 1) {
-            Best other = shfl_best(best, o, true);
-            if (better(S, other, best)) best = other;
-        }
-        if (tracer) c0b = clock64();
-        if (lane == 0) sh_best[warp] = best;
         __syncthreads();
-        if (tracer) c0c = clock64();
-        if (warp == 0) {
-            Best bb = lane < NT / 32 ? sh_best[lane] : Best{0, 0, 0};
+        if (top > 0 && sh_ntie > MAX_TIES) {
+            // very many pairs tie at the top (late in a small corpus): the general reduction, restricted to the tied entries
+            Best best{0, 0, 0};
+            for (uint32_t i = tid; i < n_scan; i += NT) {
+                const uint32_t e = use_cache ? i : __ldcg(S.live + i);
+                const long long cnt = use_cache ? (H.key[i] ? H.cnt[i] : 0) : __ldcg(S.ph_cnt + e);
+                if (cnt != top) continue;
+                Best c{top, use_cache ? H.key[i] : __ldcg(S.ph_key + e), e};
+                if (best.cnt == 0 || better(S, c, best)) best = c;
+            }
             for (int o = 16; o; o >>= 1) {
-                Best other = shfl_best(bb, o, false);
-                if (better(S, other, bb)) bb = other;
+                Best other = shfl_best(best, o, false);
+                if (other.cnt > 0 && (best.cnt == 0 || better(S, other, best))) best = other;
+            }
+            if (lane == 0) sh_bestw[warp] = best;
+            __syncthreads();
+            if (warp == 0) {
+                Best bb = lane < NT / 32 ? sh_bestw[lane] : Best{0, 0, 0};
+                for (int o = 16; o; o >>= 1) {
+                    Best other = shfl_best(bb, o, false);
+                    if (other.cnt > 0 && (bb.cnt == 0 || better(S, other, bb))) bb = other;
+                }
+                if (lane == 0) sh_win = bb;
+            }
+        } else if (warp == 0) {  // the tied entries (usually one): order by bytes
+            const uint32_t n_tie = top > 0 ? sh_ntie : 0;
+            Best bb{0, 0, 0};
+            for (uint32_t k = lane; k < n_tie; k += 32) {
+                const uint32_t e = sh_tie[k];
+                Best c{top, use_cache ? H.key[e] : __ldcg(S.ph_key + e), e};
+                if (bb.cnt == 0 || better(S, c, bb)) bb = c;
+            }
+            if (n_tie > 1) {
+                for (int o = 16; o; o >>= 1) {
+                    Best other = shfl_best(bb, o, false);
+                    if (other.cnt > 0 && (bb.cnt == 0 || better(S, other, bb))) bb = other;
+                }
             }
             if (lane == 0) sh_win = bb;
         }
@@ -690,7 +729,6 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         __syncthreads();  // cache and leader stores are ordered before the next argmax of this CTA
         if (tracer) {
             long long c5 = clock64();
-            S.ctrl->phase_clk[5] += c0a - c0; S.ctrl->phase_clk[6] += c0b - c0a; S.ctrl->phase_clk[7] += c0c - c0b;
             S.ctrl->phase_clk[0] += c1 - c0; S.ctrl->phase_clk[1] += c2 - c1; S.ctrl->phase_clk[2] += c3 - c2;
             S.ctrl->phase_clk[3] += c4 - c3; S.ctrl->phase_clk[4] += c5 - c4;
         }
@@ -877,13 +915,14 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     if (h_ctrl.dbg[5])
         fprintf(stderr, "[train watchdog] stopped at iteration %u after %u loop passes; merges %u, rebuilds %u, heavy %u\n", h_ctrl.dbg[4], h_ctrl.dbg[5],
                 h_ctrl.n_merges, h_ctrl.n_rebuilds, h_ctrl.n_heavy);
+    if (S.flags & 4u) fprintf(stderr, "[train check] token comparisons %u over %u iterations\n", h_ctrl.dbg[6], h_ctrl.n_iters);
     if (S.flags & 2u)
         fprintf(stderr, "[train check] stale cache copies %u (first at iteration %u), hot pairs missing from the cache %u (first at iteration %u), rebuilds %u, heavy %u, iterations %u\n",
                 h_ctrl.dbg[0], h_ctrl.dbg[1], h_ctrl.dbg[2], h_ctrl.dbg[3], h_ctrl.n_rebuilds, h_ctrl.n_heavy, h_ctrl.n_iters);
     if (trace_path) {  // developer aid: per-iteration timings of the loop
         fprintf(stderr, "[train trace] driver thread 0 cycles: argmax %llu, select+bookkeeping %llu, filter/wake %llu, rewrite %llu, close %llu; "
-                        "[argmax: scan %llu, warp reduce %llu, barrier %llu] rebuilds %u, heavy steps %u\n", h_ctrl.phase_clk[0], h_ctrl.phase_clk[1], h_ctrl.phase_clk[2], h_ctrl.phase_clk[3],
-                h_ctrl.phase_clk[4], h_ctrl.phase_clk[5], h_ctrl.phase_clk[6], h_ctrl.phase_clk[7], h_ctrl.n_rebuilds, h_ctrl.n_heavy);
+                        "rebuilds %u, heavy steps %u\n", h_ctrl.phase_clk[0], h_ctrl.phase_clk[1], h_ctrl.phase_clk[2], h_ctrl.phase_clk[3],
+                h_ctrl.phase_clk[4], h_ctrl.n_rebuilds, h_ctrl.n_heavy);
         std::vector<uint32_t> tr(4ull * h_ctrl.n_iters);
         cudaMemcpy(tr.data(), d_trace, tr.size() * 4, cudaMemcpyDeviceToHost);
         if (FILE* f = fopen(trace_path, "w")) {
