@@ -307,11 +307,14 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
         ids = tok.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=eng, on_device=(d_enc, n_enc))
     sync_all()
     ev0.record()
+    t_calls = [time.perf_counter()]
     for _ in range(args.steps):
         ids = tok.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=eng, on_device=(d_enc, n_enc))
+        t_calls.append(time.perf_counter())  # bpe_encode returns after its stream work: host time per call = device time
     ev1.record()
     sync_all()
     enc_ms = max_over_ranks(ev0.elapsed_time(ev1) / args.steps)
+    log("[bench] encode resident, ms per call: " + ", ".join(f"{(b - a) * 1e3:.1f}" for a, b in zip(t_calls[:-1], t_calls[1:])))
     n_ids_local = int(ids.numel())
     # roundtrip at full size: GPU decode of the ids must give back the bytes
     back = tok.decode_array(ids, engine=eng, to_host=False) if n_enc else d_enc[:0]

@@ -123,6 +123,7 @@ class Engine:
         self.ctx = ctx
         self._specials: list[bytes] | None = None
         self._model_token = None
+        self.table_log2, self.pool_bytes = 22, 256 << 20
         if table_log2 is not None or pool_bytes is not None:
             self.configure(table_log2 or 22, pool_bytes or (256 << 20))
 
@@ -151,7 +152,15 @@ class Engine:
 
     def configure(self, table_log2: int, pool_bytes: int):
         self._check(self.lib.bpe_ctx_configure(self.ctx, int(table_log2), int(pool_bytes)))
+        self.table_log2, self.pool_bytes = int(table_log2), int(pool_bytes)
         self._model_token = None
+
+    def grow(self) -> bool:
+        """Four times the table slots and pool bytes (drops what was counted); False once 2^28 slots are reached."""
+        if self.table_log2 >= 28:
+            return False
+        self.configure(self.table_log2 + 2, self.pool_bytes * 4)
+        return True
 
     def set_profiling(self, on: bool):
         self._check(self.lib.bpe_set_profiling(self.ctx, 1 if on else 0))

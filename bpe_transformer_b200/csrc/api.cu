@@ -51,7 +51,7 @@ int ctx_status_to_code(bpe_ctx* ctx, uint32_t st) {
 static void free_unique(bpe_ctx* ctx) {
     if (!ctx->ut_alloc) return;
     cudaFree(ctx->ut.key); cudaFree(ctx->ut.cnt); cudaFree(ctx->ut.pool_off); cudaFree(ctx->ut.len); cudaFree(ctx->ut.chk);
-    cudaFree(ctx->ut.enc_off); cudaFree(ctx->ut.enc_len); cudaFree(ctx->ut.pool); cudaFree(ctx->ut.counters);
+    cudaFree(ctx->ut.enc_off); cudaFree(ctx->ut.enc_len); cudaFree(ctx->ut.enc); cudaFree(ctx->ut.pool); cudaFree(ctx->ut.counters);
     ctx->ut = UniqueTable{};
     ctx->ut_alloc = false;
 }
@@ -62,8 +62,10 @@ static int clear_unique(bpe_ctx* ctx) {
     CUDA_TRY(ctx, cudaMemset(ctx->ut.cnt, 0, cap * 8));
     CUDA_TRY(ctx, cudaMemset(ctx->ut.chk, 0, cap * 4));
     CUDA_TRY(ctx, cudaMemset(ctx->ut.enc_len, 0xFF, cap * 4));
+    CUDA_TRY(ctx, cudaMemset(ctx->ut.enc, 0, cap * 16));
     CUDA_TRY(ctx, cudaMemset(ctx->ut.counters, 0, 4 * 8));
     ctx->enc_done = 0;
+    ctx->enc_warm = false;
     return BPE_OK;
 }
 
@@ -78,6 +80,7 @@ static int ensure_unique(bpe_ctx* ctx) {
     CUDA_TRY(ctx, cudaMalloc(&t.chk, cap * 4));
     CUDA_TRY(ctx, cudaMalloc(&t.enc_off, cap * 4));
     CUDA_TRY(ctx, cudaMalloc(&t.enc_len, cap * 4));
+    CUDA_TRY(ctx, cudaMalloc(&t.enc, cap * 16));
     CUDA_TRY(ctx, cudaMalloc(&t.pool, ctx->pool_bytes + BPE_TEXT_PAD));
     CUDA_TRY(ctx, cudaMalloc(&t.counters, 4 * 8));
     t.cap_mask = cap - 1;
@@ -277,8 +280,10 @@ int bpe_load_model(bpe_ctx* ctx, const uint32_t* h_a, const uint32_t* h_b, const
     // cached encodings belong to the previous model
     size_t ucap = ctx->ut.cap_mask + 1;
     CUDA_TRY(ctx, cudaMemset(ctx->ut.enc_len, 0xFF, ucap * 4));
+    CUDA_TRY(ctx, cudaMemset(ctx->ut.enc, 0, ucap * 16));
     CUDA_TRY(ctx, cudaMemset(ctx->ut.counters + 3, 0, 8));
     ctx->enc_done = 0;
+    ctx->enc_warm = false;
     ctx->model_loaded = true;
     return BPE_OK;
 }

@@ -20,6 +20,7 @@ enum : uint32_t {
     ST_PAIR_TABLE_FULL = 1u << 5,
     ST_LIST_FULL = 1u << 6,
     ST_WATCHDOG = 1u << 7,
+    ST_ENC_MISS = 1u << 8,  // encode: a pretoken of the text is not in the table yet (handled inside bpe_encode)
 };
 
 // ---- code-point classes (include/bpe_unicode_tables.h) --------------------------------------------------
@@ -111,6 +112,16 @@ __device__ __forceinline__ TokenKey hash_bytes(const uint8_t* __restrict__ base,
     return k;
 }
 
+// Key only (the check word is recomputed when a shared-table entry is folded into the global table).
+__device__ __forceinline__ uint64_t hash_key(const uint8_t* __restrict__ base, uint64_t p, uint32_t len) {
+    uint64_t h = 0x243F6A8885A308D3ull ^ ((uint64_t)len * 0x9E3779B97F4A7C15ull);
+    uint32_t o = 0;
+    for (; o + 8 <= len; o += 8) h = mix64(h, load_u64_unaligned(base, p + o));
+    if (o < len) h = mix64(h, load_u64_unaligned(base, p + o) & ((1ull << ((len - o) * 8)) - 1ull));
+    h ^= h >> 29;
+    return h ? h : 1ull;
+}
+
 // ---- the table of distinct pretokens (context-owned, global memory) ---------------------------------------
 struct UniqueTable {
     uint64_t* key;       // [cap] 0 = empty
@@ -120,6 +131,9 @@ struct UniqueTable {
     uint32_t* chk;       // [cap] 0 until the inserting thread has published
     uint32_t* enc_off;   // [cap] offset of the cached encoding in the id pool (encode path)
     uint32_t* enc_len;   // [cap] 0xFFFFFFFF = not encoded yet
+    uint4* enc;          // [cap] what the emit pass reads, one 16-byte load per probe: {key lo, key hi, w0, w1}, key 0 = empty.
+                         //       w1 bit 31 clear: w1 ids at id-pool offset w0.  bit 31 set: (w1 >> 16) & 0x3FFF ids stored in place:
+                         //       bit 30 set -> the single id w0; else 16-bit ids w0 & 0xFFFF, w0 >> 16, w1 & 0xFFFF.
     uint8_t* pool;
     uint64_t cap_mask;
     uint64_t pool_cap;
@@ -178,6 +192,42 @@ __device__ __forceinline__ uint64_t unique_find(const UniqueTable& t, TokenKey k
     return ~0ull;
 }
 
+// fb = up to four distinct first bytes of the special tokens packed in a word (0xFF = unused), so that the common
+// "not a special token" answer costs a few register compares instead of an indexed read of the kernel parameters.
+// Index of the special token equal to text[p, p + len), -1 if it is ordinary text.
+__device__ __forceinline__ int special_index(const Specials& sp, uint32_t fb, const uint8_t* __restrict__ text, uint64_t p, uint64_t len) {
+    const uint32_t b0 = text[p];
+    if (fb != 0xFFFFFFFEu) {
+        if (b0 != (fb & 0xFF) && b0 != ((fb >> 8) & 0xFF) && b0 != ((fb >> 16) & 0xFF) && b0 != (fb >> 24)) return -1;
+    } else if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return -1;
+    for (int s = 0; s < sp.n; s++) {
+        if (sp.off[s + 1] - sp.off[s] != len) continue;
+        bool ok = true;
+        for (uint32_t k = 0; k < len && ok; k++) ok = text[p + k] == sp.blob[sp.off[s] + k];
+        if (ok) return s;
+    }
+    return -1;
+}
+
+__device__ __forceinline__ bool token_is_special(const Specials& sp, uint32_t fb, const uint8_t* __restrict__ text, uint64_t p, uint64_t len) {
+    return special_index(sp, fb, text, p, len) >= 0;
+}
+
+__device__ __forceinline__ uint32_t special_first_bytes(const Specials& sp) {
+    uint32_t fb = 0xFFFFFFFFu;
+    int used = 0;
+    for (int s = 0; s < sp.n; s++) {
+        uint32_t b = sp.blob[sp.off[s]];
+        bool seen = false;
+        for (int k = 0; k < used; k++) seen |= ((fb >> (8 * k)) & 0xFF) == b;
+        if (seen) continue;
+        if (used == 4 || b == 0xFF) return 0xFFFFFFFEu;  // too many / ambiguous: use the 256-bit set
+        fb = (fb & ~(0xFFu << (8 * used))) | (b << (8 * used));
+        used++;
+    }
+    return fb;
+}
+
 // ---- bit helpers -----------------------------------------------------------------------------------------
 // End (exclusive) of the token that starts at bit `b` of start word `w` (word index wi), scanning forward.
 __device__ __forceinline__ uint64_t token_end(const uint32_t* __restrict__ start, uint64_t n_words, uint64_t wi, uint32_t w,
@@ -221,6 +271,7 @@ struct bpe_ctx {
     uint32_t* d_idpool = nullptr;      // cached encodings of distinct pretokens
     uint64_t idpool_cap = 0;
     uint64_t enc_done = 0;             // number of distinct pretokens already encoded
+    bool enc_warm = false;             // the last bpe_encode found every pretoken in the table: try without counting first
     // scratch reused across calls
     void* scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};

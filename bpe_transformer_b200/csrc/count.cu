@@ -37,37 +37,6 @@ struct SharedTable {
 
 #define COUNT_SMEM (sizeof(SharedTable) + (COUNT_THREADS / 32) * 1056 * sizeof(unsigned short))
 
-// fb = up to four distinct first bytes of the special tokens packed in a word (0xFF = unused), so that the common
-// "not a special token" answer costs a few register compares instead of an indexed read of the kernel parameters.
-__device__ __forceinline__ bool token_is_special(const Specials& sp, uint32_t fb, const uint8_t* __restrict__ text, uint64_t p, uint64_t len) {
-    const uint32_t b0 = text[p];
-    if (fb != 0xFFFFFFFEu) {
-        if (b0 != (fb & 0xFF) && b0 != ((fb >> 8) & 0xFF) && b0 != ((fb >> 16) & 0xFF) && b0 != (fb >> 24)) return false;
-    } else if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return false;
-    for (int s = 0; s < sp.n; s++) {
-        if (sp.off[s + 1] - sp.off[s] != len) continue;
-        bool ok = true;
-        for (uint32_t k = 0; k < len && ok; k++) ok = text[p + k] == sp.blob[sp.off[s] + k];
-        if (ok) return true;
-    }
-    return false;
-}
-
-__device__ __forceinline__ uint32_t special_first_bytes(const Specials& sp) {
-    uint32_t fb = 0xFFFFFFFFu;
-    int used = 0;
-    for (int s = 0; s < sp.n; s++) {
-        uint32_t b = sp.blob[sp.off[s]];
-        bool seen = false;
-        for (int k = 0; k < used; k++) seen |= ((fb >> (8 * k)) & 0xFF) == b;
-        if (seen) continue;
-        if (used == 4 || b == 0xFF) return 0xFFFFFFFEu;  // too many / ambiguous: use the 256-bit set
-        fb = (fb & ~(0xFFu << (8 * used))) | (b << (8 * used));
-        used++;
-    }
-    return fb;
-}
-
 // Adds c to the count of an already-known key; false if the key is not in the table yet.
 __device__ __forceinline__ bool unique_bump(const UniqueTable& t, uint64_t key, uint64_t c) {
     uint64_t slot = (key * 0xD6E8FEB86659FD93ull >> 17) & t.cap_mask;
@@ -81,16 +50,6 @@ __device__ __forceinline__ bool unique_bump(const UniqueTable& t, uint64_t key, 
         slot = (slot + 1) & t.cap_mask;
     }
     return false;
-}
-
-// Key only (the check word is recomputed when a shared-table entry is folded into the global table).
-__device__ __forceinline__ uint64_t hash_key(const uint8_t* __restrict__ base, uint64_t p, uint32_t len) {
-    uint64_t h = 0x243F6A8885A308D3ull ^ ((uint64_t)len * 0x9E3779B97F4A7C15ull);
-    uint32_t o = 0;
-    for (; o + 8 <= len; o += 8) h = mix64(h, load_u64_unaligned(base, p + o));
-    if (o < len) h = mix64(h, load_u64_unaligned(base, p + o) & ((1ull << ((len - o) * 8)) - 1ull));
-    h ^= h >> 29;
-    return h ? h : 1ull;
 }
 
 // A warp takes 32 mask words (1 KiB of text) per round.  The set bits of the 32 words are spread evenly over the

@@ -6,10 +6,14 @@
 //   2. encode_new_kernel: one WARP per pretoken that has no cached encoding yet: byte ids, then repeatedly
 //      join the leftmost adjacent pair of minimum merge rank ((a, b) -> (rank, id) hash, L2-resident) — the
 //      literal rule of _find_pair_in_merges (:257-290), one occurrence per round;
-//   3. emit: per 32-byte chunk look every token up (key -> slot -> cached ids), count the ids, prefix-sum the
-//      counts (per tile in shared memory, across tiles with a small scan kernel), write the ids in text order
-//      as uint16 or uint32.
+//   3. emit_fused_kernel: one pass over the text; a warp per 1 KiB window looks every token up (key -> 16-byte table
+//      entry holding up to three ids in place), the windows' id counts are prefix-summed with a chained scan
+//      (decoupled look-back), and the ids are written in text order as uint16 or uint32.
+// Once a text's pretokens are all cached (a second file of the same language, the next shard), step 1's count and step 2
+// are skipped: the emit pass itself reports a pretoken it does not know and only then is the text counted.
 // Special tokens map straight to their id (:172-176).  No communication between GPUs: shards are independent.
+#include <algorithm>
+
 #include "common.cuh"
 
 #define ENC_THREADS 256
@@ -43,12 +47,12 @@ __global__ void list_new_kernel(UniqueTable ut, uint32_t* __restrict__ list, uns
 }
 
 // ---- step 2b: one warp per new pretoken -------------------------------------------------------------------------
-__global__ void __launch_bounds__(ENC_THREADS) encode_new_kernel(UniqueTable ut, const uint32_t* __restrict__ list, uint64_t n_list,
-                                                                 MergeTable M, const uint32_t* __restrict__ byte_to_id,
+__global__ void __launch_bounds__(ENC_THREADS) encode_new_kernel(UniqueTable ut, const uint32_t* __restrict__ list,
+                                                                 const unsigned long long* __restrict__ n_list_dev, MergeTable M, const uint32_t* __restrict__ byte_to_id,
                                                                  uint32_t* __restrict__ idpool, uint64_t idpool_cap, uint32_t* status) {
     const uint32_t lane = threadIdx.x & 31;
     const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
-    if (warp >= n_list) return;
+    if (warp >= *n_list_dev) return;  // the grid is sized for the upper bound "distinct pretokens not seen by an earlier call"
     const uint32_t slot = list[warp];
     const uint32_t len = ut.len[slot];
     const uint8_t* src = ut.pool + ut.pool_off[slot];
@@ -57,11 +61,16 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_new_kernel(UniqueTable ut,
     base = __shfl_sync(0xFFFFFFFFu, base, 0);
     if (base + len > idpool_cap) { if (lane == 0) set_status(status, ST_POOL_FULL); return; }
     uint32_t* ids = idpool + base;
+    // A pretoken that cannot be encoded (a byte or a merged pair without an id: KeyError at bpe_tokenizer.py:206 / :290)
+    // is left unpublished and nothing is raised here: the table may hold pretokens of earlier texts.  The emit pass raises
+    // when the text being encoded really contains it, on every call.
+    bool bad = false;
     for (uint32_t i = lane; i < len; i += 32) {
         uint32_t id = __ldg(byte_to_id + src[i]);
-        if (id == 0xFFFFFFFFu) set_status(status, ST_MISSING_ID);
+        if (id == 0xFFFFFFFFu) bad = true;
         ids[i] = id;
     }
+    bad = __any_sync(0xFFFFFFFFu, bad);
     __syncwarp();
     uint32_t cur = len;
     while (cur >= 2) {
@@ -81,7 +90,7 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_new_kernel(UniqueTable ut,
             if (ob < best) { best = ob; best_id = oid; }
         }
         if (best == ~0ull) break;
-        if (best_id == 0xFFFFFFFFu) { if (lane == 0) set_status(status, ST_MISSING_ID); break; }  // KeyError at bpe_tokenizer.py:290
+        if (best_id == 0xFFFFFFFFu) { bad = true; break; }
         uint32_t at = (uint32_t)best;
         // ids[at] = merged; close the gap at at+1 (chunks of 32, each read before it is overwritten)
         if (lane == 0) ids[at] = best_id;
@@ -95,7 +104,16 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_new_kernel(UniqueTable ut,
         cur--;
         __syncwarp();
     }
-    if (lane == 0) { ut.enc_off[slot] = (uint32_t)base; ut.enc_len[slot] = cur; }
+    if (lane == 0 && !bad) {
+        ut.enc_off[slot] = (uint32_t)base;
+        ut.enc_len[slot] = cur;
+        const uint64_t key = ut.key[slot];
+        uint32_t w0 = (uint32_t)base, w1 = cur;
+        const uint32_t i0 = ids[0], i1 = cur > 1 ? ids[1] : 0u, i2 = cur > 2 ? ids[2] : 0u;
+        if (cur <= 3 && (i0 | i1 | i2) <= 0xFFFFu) { w0 = i0 | (i1 << 16); w1 = 0x80000000u | (cur << 16) | i2; }
+        else if (cur == 1) { w0 = i0; w1 = 0xC0010000u; }
+        ut.enc[slot] = make_uint4((uint32_t)key, (uint32_t)(key >> 32), w0, w1);
+    }
 }
 
 struct EmitParams {
@@ -109,61 +127,7 @@ struct EmitParams {
     uint32_t* status;
 };
 
-// Visits the tokens that start in mask word wi; calls f(ids pointer or null, count, special id).
-template <class F>
-__device__ __forceinline__ void for_each_token(const EmitParams& P, const Specials& sp, uint64_t wi, uint32_t w, F f) {
-    for (uint32_t m = w; m; m &= m - 1) {
-        uint32_t b = __ffs(m) - 1;
-        uint64_t p = wi * 32 + b;
-        uint64_t e = token_end(P.start, P.n_words, wi, w, b, P.n);
-        uint64_t len = e - p;
-        int s = -1;
-        if (sp.n) {
-            uint8_t b0 = P.text[p];
-            if ((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)
-                for (int k = 0; k < sp.n && s < 0; k++) {
-                    if (sp.off[k + 1] - sp.off[k] != len) continue;
-                    bool ok = true;
-                    for (uint32_t q = 0; q < len && ok; q++) ok = P.text[p + q] == sp.blob[sp.off[k] + q];
-                    if (ok) s = k;
-                }
-        }
-        if (s >= 0) {
-            uint32_t sid = __ldg(P.special_id + s);
-            if (sid == 0xFFFFFFFFu) set_status(P.status, ST_MISSING_ID);  // KeyError at bpe_tokenizer.py:175
-            f((const uint32_t*)nullptr, 1u, sid);
-            continue;
-        }
-        uint64_t slot = unique_find(P.ut, hash_bytes(P.text, p, len));
-        if (slot == ~0ull) { set_status(P.status, ST_TABLE_FULL); continue; }
-        f(P.idpool + P.ut.enc_off[slot], P.ut.enc_len[slot], 0u);
-    }
-}
-
-// ---- step 3a: ids per tile --------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(ENC_THREADS) emit_count_kernel(const EmitParams P, const __grid_constant__ Specials sp,
-                                                                 uint32_t* __restrict__ tile_total, uint8_t* __restrict__ chunk_cnt) {
-    __shared__ uint32_t warp_sum[ENC_THREADS / 32];
-    const uint64_t wi = blockIdx.x * (uint64_t)ENC_THREADS + threadIdx.x;
-    uint32_t mine = 0;
-    if (wi < P.n_words) {
-        uint32_t w = __ldg(P.start + wi);
-        for_each_token(P, sp, wi, w, [&](const uint32_t*, uint32_t cnt, uint32_t) { mine += cnt; });
-        // a chunk of 32 bytes holds at most 32 tokens but one token can have thousands of ids: saturate, recount on emit
-        chunk_cnt[wi] = mine < 255 ? (uint8_t)mine : 255;
-    }
-    uint32_t v = mine;
-    for (int o = 16; o; o >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, o);
-    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = v;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t t = 0;
-        for (int k = 0; k < ENC_THREADS / 32; k++) t += warp_sum[k];
-        tile_total[blockIdx.x] = t;
-    }
-}
-
-// ---- step 3b: exclusive scan of the tile totals (one CTA; n_tiles is small: text bytes / 8192) -------------------
+// ---- exclusive scan of per-tile totals (decode; one CTA, the number of tiles is small) --------------------------------
 __global__ void __launch_bounds__(1024) scan_totals_kernel(const uint32_t* __restrict__ in, uint64_t n, uint64_t* __restrict__ out) {
     __shared__ uint64_t warp_tot[32];
     __shared__ uint64_t carry_s;
@@ -197,39 +161,157 @@ __global__ void __launch_bounds__(1024) scan_totals_kernel(const uint32_t* __res
     if (threadIdx.x == 0) out[n] = carry_s;
 }
 
-// ---- step 3c: write the ids ---------------------------------------------------------------------------------------
-template <typename OutT>
-__global__ void __launch_bounds__(ENC_THREADS) emit_write_kernel(const EmitParams P, const __grid_constant__ Specials sp,
-                                                                 const uint64_t* __restrict__ tile_off, const uint8_t* __restrict__ chunk_cnt,
-                                                                 OutT* __restrict__ out) {
-    __shared__ uint32_t warp_sum[ENC_THREADS / 32];
-    const uint64_t wi = blockIdx.x * (uint64_t)ENC_THREADS + threadIdx.x;
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t w = 0, mine = 0;
-    if (wi < P.n_words) {
-        w = __ldg(P.start + wi);
-        mine = chunk_cnt[wi];
-        if (mine == 255) {  // saturated: recount
-            mine = 0;
-            for_each_token(P, sp, wi, w, [&](const uint32_t*, uint32_t cnt, uint32_t) { mine += cnt; });
+// ---- single-pass emit: look every token up once, place the ids with a chained scan over 1 KiB windows -----------------
+// A warp takes a window of 32 mask words (tickets are handed out in increasing order), spreads the window's tokens over
+// its lanes, looks each one up (key -> table slot -> cached ids), publishes the window's id count, obtains the count of
+// all earlier windows by looking back at their published states (decoupled look-back), and writes its ids.
+// HBM traffic: N bytes of text + N/8 of mask read, 2T (or 4T) bytes of ids written; the tables sit in L2.
+#define EMIT_THREADS 256
+#define EMIT_WARPS (EMIT_THREADS / 32)
+#define EMIT_KEEP 512        // tokens of a window whose table entries are kept in shared memory between the two passes
+#define ST_AGG (1ull << 62)  // state word: window's own count is available
+#define ST_INC (2ull << 62)  // state word: count of this and all earlier windows is available
+
+struct EmitWarp {
+    uint2 ent[EMIT_KEEP];       // (w0, w1) of UniqueTable::enc per token; a window with more tokens looks the rest up twice
+    unsigned short pos[1056];   // start positions inside the window
+};
+
+struct EmitLookup {
+    const EmitParams& P;
+    const Specials& sp;
+    uint32_t fb;
+    // (w0, w1) as in UniqueTable::enc; a miss gives zero ids and raises ST_ENC_MISS
+    __device__ __forceinline__ uint2 operator()(uint64_t p, uint64_t len) const {
+        if (sp.n) {
+            const int s = special_index(sp, fb, P.text, p, len);
+            if (s >= 0) {
+                const uint32_t id = __ldg(P.special_id + s);
+                if (id == 0xFFFFFFFFu) set_status(P.status, ST_MISSING_ID);  // KeyError at bpe_tokenizer.py:175
+                return make_uint2(id, 0xC0010000u);
+            }
         }
+        if (len < 0xFFFFFFFFull) {
+            const uint64_t key = hash_key(P.text, p, (uint32_t)len);
+            uint64_t slot = (key * 0xD6E8FEB86659FD93ull >> 17) & P.ut.cap_mask;  // the slot sequence of unique_find
+            for (uint64_t probe = 0; probe <= P.ut.cap_mask; probe++) {
+                const uint4 e = __ldg(P.ut.enc + slot);
+                if (e.x == (uint32_t)key && e.y == (uint32_t)(key >> 32)) return make_uint2(e.z, e.w);
+                if ((e.x | e.y) == 0) break;
+                slot = (slot + 1) & P.ut.cap_mask;
+            }
+        }
+        set_status(P.status, ST_ENC_MISS);  // not counted / not encoded yet: the host counts the text and runs the pass again
+        return make_uint2(0u, 0u);
     }
-    uint32_t x = mine;
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
-        if (lane >= (unsigned)o) x += y;
+};
+
+__device__ __forceinline__ uint32_t ent_ids(uint2 e) { return (e.y >> 31) ? ((e.y >> 16) & 0x3FFFu) : e.y; }
+
+template <typename OutT>
+__global__ void __launch_bounds__(EMIT_THREADS, 4) emit_fused_kernel(const EmitParams P, const __grid_constant__ Specials sp, uint64_t n_windows,
+                                                                     unsigned long long* __restrict__ state, unsigned long long* __restrict__ ticket,
+                                                                     OutT* __restrict__ out, uint64_t cap, unsigned long long* __restrict__ total_out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    EmitWarp& W = reinterpret_cast<EmitWarp*>(smem_raw)[threadIdx.x >> 5];
+    const uint32_t lane = threadIdx.x & 31;
+    const EmitLookup lookup{P, sp, special_first_bytes(sp)};
+    for (;;) {
+        unsigned long long win = 0;
+        if (lane == 0) win = atomicAdd(ticket, 1ull);
+        win = __shfl_sync(0xFFFFFFFFu, win, 0);
+        if (win >= n_windows) return;
+        const uint64_t w0 = win * 32, wi = w0 + lane, kib = w0 * 32;
+        const uint32_t w = wi < P.n_words ? __ldg(P.start + wi) : 0u;
+        const uint32_t mine = __popc(w);
+        uint32_t incl = mine;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= (uint32_t)o) incl += y;
+        }
+        const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        uint32_t at = incl - mine;
+        for (uint32_t m = w; m; m &= m - 1) W.pos[at++] = (unsigned short)(lane * 32 + (__ffs(m) - 1));
+        uint64_t tail_end = 0;
+        if (total) {
+            const uint32_t last_lane = 31 - __clz(__ballot_sync(0xFFFFFFFFu, w != 0));
+            if (lane == last_lane) tail_end = token_end(P.start, P.n_words, wi, w, 31 - __clz(w), P.n);
+            tail_end = __shfl_sync(0xFFFFFFFFu, tail_end, last_lane);
+        }
+        __syncwarp();
+        // ---- look every token up -------------------------------------------------------------------------------------
+        uint32_t my_ids = 0;
+        for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+            __syncwarp();
+            const uint32_t t = t0 + lane;
+            if (t >= total) continue;
+            const uint64_t p = kib + W.pos[t];
+            const uint64_t e = (t + 1 < total) ? kib + W.pos[t + 1] : tail_end;
+            const uint2 ent = lookup(p, e - p);
+            if (t < EMIT_KEEP) W.ent[t] = ent;
+            my_ids += ent_ids(ent);
+        }
+        __syncwarp();
+        unsigned long long win_ids = my_ids;
+        for (int o = 16; o; o >>= 1) win_ids += __shfl_xor_sync(0xFFFFFFFFu, win_ids, o);
+        // ---- chained scan over the windows ---------------------------------------------------------------------------------
+        unsigned long long before = 0;
+        if (win == 0) {
+            if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state) = ST_INC | win_ids;
+        } else {
+            if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state + win) = ST_AGG | win_ids;
+            long long j0 = (long long)win - 1;  // lane L looks at window j0 - L
+            for (;;) {
+                const long long j = j0 - (long long)lane;
+                unsigned long long v = j >= 0 ? *reinterpret_cast<volatile unsigned long long*>(state + j) : ST_INC;  // in front of window 0: prefix 0
+                const uint32_t inc = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 2), none = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 0);
+                const uint32_t first_inc = inc ? (uint32_t)__ffs(inc) - 1 : 32;  // nearest window whose inclusive prefix is known
+                const uint32_t need = first_inc >= 31 ? 0xFFFFFFFFu : ((2u << first_inc) - 1u);
+                if (none & need) continue;  // a window we depend on has not published yet: look again
+                unsigned long long part = (lane <= first_inc) ? (v & ~(3ull << 62)) : 0ull;
+                for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
+                before += part;
+                if (first_inc < 32) break;
+                j0 -= 32;
+            }
+            if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state + win) = ST_INC | (before + win_ids);
+        }
+        if (win == n_windows - 1 && lane == 0) *total_out = before + win_ids;
+        // ---- write the ids -----------------------------------------------------------------------------------------------------
+        unsigned long long running = before;
+        for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+            const uint32_t t = t0 + lane;
+            uint2 ent = make_uint2(0u, 0u);
+            if (t < total) {
+                if (t < EMIT_KEEP) ent = W.ent[t];
+                else {
+                    const uint64_t p = kib + W.pos[t];
+                    ent = lookup(p, ((t + 1 < total) ? kib + W.pos[t + 1] : tail_end) - p);
+                }
+            }
+            const uint32_t n_ids = ent_ids(ent);
+            uint32_t x = n_ids;
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+                if (lane >= (uint32_t)o) x += y;
+            }
+            const unsigned long long dst = running + x - n_ids;
+            if (n_ids) {
+                if (!(ent.y >> 31)) {
+                    const uint32_t* ids = P.idpool + ent.x;
+                    for (uint32_t k = 0; k < n_ids; k++) if (dst + k < cap) out[dst + k] = (OutT)__ldg(ids + k);
+                } else if (ent.y & 0x40000000u) {
+                    if (dst < cap) out[dst] = (OutT)ent.x;
+                } else {
+                    if (dst < cap) out[dst] = (OutT)(ent.x & 0xFFFFu);
+                    if (n_ids > 1 && dst + 1 < cap) out[dst + 1] = (OutT)(ent.x >> 16);
+                    if (n_ids > 2 && dst + 2 < cap) out[dst + 2] = (OutT)(ent.y & 0xFFFFu);
+                }
+            }
+            running += __shfl_sync(0xFFFFFFFFu, x, 31);
+        }
+        __syncwarp();
     }
-    if (lane == 31) warp_sum[warp] = x;
-    __syncthreads();
-    uint32_t before = 0;
-    for (uint32_t k = 0; k < warp; k++) before += warp_sum[k];
-    uint64_t at = tile_off[blockIdx.x] + before + x - mine;
-    if (wi < P.n_words && mine)
-        for_each_token(P, sp, wi, w, [&](const uint32_t* ids, uint32_t cnt, uint32_t special) {
-            if (!ids) { out[at++] = (OutT)special; return; }
-            for (uint32_t k = 0; k < cnt; k++) out[at + k] = (OutT)ids[k];
-            at += cnt;
-        });
 }
 
 // ---- decode: ids -> bytes (bpe_tokenizer.py:119-137; U+FFFD for unknown ids) -------------------------------------------
@@ -285,14 +367,7 @@ __global__ void __launch_bounds__(ENC_THREADS) decode_write_kernel(const IdT* __
 
 }  // namespace
 
-int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, void* d_out, int out_elem_bytes,
-               uint64_t cap, uint64_t* n_out, cudaStream_t s) {
-    *n_out = 0;
-    if (n == 0) return BPE_OK;
-    // 1. every pretoken of the text into the table (the memo)
-    int rc = launch_count(ctx, d_text, n, d_start, s);
-    if (rc) return rc;
-    // 2. encode the pretokens that are new
+static int encode_new_pretokens(bpe_ctx* ctx, cudaStream_t s) {
     uint64_t slots = ctx->ut.cap_mask + 1;
     uint64_t h_counters[4];
     CUDA_TRY(ctx, cudaMemcpyAsync(h_counters, ctx->ut.counters, sizeof(h_counters), cudaMemcpyDeviceToHost, s));
@@ -300,62 +375,82 @@ int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* 
     uint32_t st = ctx_read_status(ctx, s);
     if (st) return ctx_status_to_code(ctx, st);
     const uint64_t n_unique = h_counters[1];
+    if (n_unique <= ctx->enc_done) return BPE_OK;
     MergeTable M{ctx->d_mkey, ctx->d_mrank, ctx->d_mid, ctx->m_mask};
-    if (n_unique > ctx->enc_done) {
-        uint64_t n_new = n_unique - ctx->enc_done;
-        uint32_t* list = (uint32_t*)ctx_scratch(ctx, 2, n_new * 4 + 16);
-        unsigned long long* n_list = (unsigned long long*)ctx_scratch(ctx, 0, 16);
-        if (!list || !n_list) return BPE_ERR_CUDA;
-        CUDA_TRY(ctx, cudaMemsetAsync(n_list, 0, 8, s));
-        {
-            KernelTimer t(ctx, "list_new_kernel", s);
-            list_new_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, s>>>(ctx->ut, list, n_list);
-            CUDA_TRY(ctx, cudaGetLastError());
-        }
-        {
-            KernelTimer t(ctx, "encode_new_kernel", s);
-            uint64_t blocks = (n_new * 32 + ENC_THREADS - 1) / ENC_THREADS;
-            encode_new_kernel<<<(unsigned)blocks, ENC_THREADS, 0, s>>>(ctx->ut, list, n_new, M, ctx->d_byte_to_id, ctx->d_idpool,
-                                                                       ctx->idpool_cap, ctx->d_status);
-            CUDA_TRY(ctx, cudaGetLastError());
-        }
-        ctx->enc_done = n_unique;
+    uint64_t n_new = n_unique - ctx->enc_done;
+    uint32_t* list = (uint32_t*)ctx_scratch(ctx, 2, n_new * 4 + 16);
+    unsigned long long* n_list = (unsigned long long*)ctx_scratch(ctx, 0, 16);
+    if (!list || !n_list) return BPE_ERR_CUDA;
+    CUDA_TRY(ctx, cudaMemsetAsync(n_list, 0, 8, s));
+    {
+        KernelTimer t(ctx, "list_new_kernel", s);
+        list_new_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, s>>>(ctx->ut, list, n_list);
+        CUDA_TRY(ctx, cudaGetLastError());
     }
-    // 3. emit
+    {
+        KernelTimer t(ctx, "encode_new_kernel", s);
+        uint64_t blocks = (n_new * 32 + ENC_THREADS - 1) / ENC_THREADS;
+        encode_new_kernel<<<(unsigned)blocks, ENC_THREADS, 0, s>>>(ctx->ut, list, n_list, M, ctx->d_byte_to_id, ctx->d_idpool, ctx->idpool_cap,
+                                                                   ctx->d_status);
+        CUDA_TRY(ctx, cudaGetLastError());
+    }
+    ctx->enc_done = n_unique;
+    return BPE_OK;
+}
+
+int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, void* d_out, int out_elem_bytes,
+               uint64_t cap, uint64_t* n_out, cudaStream_t s) {
+    *n_out = 0;
+    if (n == 0) return BPE_OK;
     EmitParams P;
     P.text = d_text; P.n = n; P.start = d_start; P.n_words = (n + 31) / 32; P.ut = ctx->ut; P.idpool = ctx->d_idpool;
     P.special_id = ctx->d_special_id; P.status = ctx->d_status;
-    const uint64_t n_tiles = (P.n_words + ENC_THREADS - 1) / ENC_THREADS;
-    uint8_t* buf = (uint8_t*)ctx_scratch(ctx, 3, n_tiles * 4 + (n_tiles + 1) * 8 + P.n_words + 64);
+    const uint64_t n_windows = (P.n_words + 31) / 32;
+    unsigned long long* buf = (unsigned long long*)ctx_scratch(ctx, 3, (n_windows + 4) * 8);
     if (!buf) return BPE_ERR_CUDA;
-    uint64_t* tile_off = (uint64_t*)buf;
-    uint32_t* tile_total = (uint32_t*)(buf + (n_tiles + 1) * 8);
-    uint8_t* chunk_cnt = buf + (n_tiles + 1) * 8 + n_tiles * 4;
-    {
-        KernelTimer t(ctx, "emit_count_kernel", s);
-        emit_count_kernel<<<(unsigned)n_tiles, ENC_THREADS, 0, s>>>(P, ctx->sp, tile_total, chunk_cnt);
-        CUDA_TRY(ctx, cudaGetLastError());
+    unsigned long long* ticket = buf, *total_out = buf + 1, *state = buf + 2;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CUDA_TRY(ctx, cudaFuncSetAttribute(emit_fused_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(EMIT_WARPS * sizeof(EmitWarp))));
+        CUDA_TRY(ctx, cudaFuncSetAttribute(emit_fused_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(EMIT_WARPS * sizeof(EmitWarp))));
+        attr_set = true;
     }
-    {
-        KernelTimer t(ctx, "scan_totals_kernel", s);
-        scan_totals_kernel<<<1, 1024, 0, s>>>(tile_total, n_tiles, tile_off);
-        CUDA_TRY(ctx, cudaGetLastError());
+    // With a warm table (every pretoken of earlier texts is cached with its ids) the text goes straight to the emit pass;
+    // if it meets a pretoken it does not know, the text is counted, the new pretokens are encoded, and the emit runs again.
+    bool counted = false;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        if (!ctx->enc_warm || attempt == 1) {
+            int rc = launch_count(ctx, d_text, n, d_start, s);
+            if (rc) return rc;
+            rc = encode_new_pretokens(ctx, s);
+            if (rc) return rc;
+            counted = true;
+        }
+        CUDA_TRY(ctx, cudaMemsetAsync(buf, 0, (n_windows + 4) * 8, s));
+        {
+            KernelTimer t(ctx, "emit_fused_kernel", s);
+            const uint64_t blocks = std::min<uint64_t>((n_windows + EMIT_WARPS - 1) / EMIT_WARPS, (uint64_t)BPE_N_SM * 4);
+            const size_t smem = EMIT_WARPS * sizeof(EmitWarp);
+            if (out_elem_bytes == 2) emit_fused_kernel<uint16_t><<<(unsigned)blocks, EMIT_THREADS, smem, s>>>(P, ctx->sp, n_windows, state, ticket, (uint16_t*)d_out, cap, total_out);
+            else emit_fused_kernel<uint32_t><<<(unsigned)blocks, EMIT_THREADS, smem, s>>>(P, ctx->sp, n_windows, state, ticket, (uint32_t*)d_out, cap, total_out);
+            CUDA_TRY(ctx, cudaGetLastError());
+        }
+        unsigned long long total = 0;
+        CUDA_TRY(ctx, cudaMemcpyAsync(&total, total_out, 8, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(ctx, cudaStreamSynchronize(s));
+        uint32_t st = ctx_read_status(ctx, s);
+        if ((st & ST_ENC_MISS) && !counted) { ctx->enc_warm = false; continue; }  // cold table: count, then emit again
+        if (st & ~ST_ENC_MISS) { ctx->enc_warm = false; return ctx_status_to_code(ctx, st & ~ST_ENC_MISS); }
+        if (st & ST_ENC_MISS) {  // counted, yet without an encoding: encode_new_kernel could not encode it
+            ctx->enc_warm = false;
+            return ctx_status_to_code(ctx, ST_MISSING_ID);
+        }
+        ctx->enc_warm = true;
+        *n_out = total;
+        if (total > cap) return ctx_fail(ctx, BPE_ERR_CAPACITY, "output buffer too small");
+        return BPE_OK;
     }
-    uint64_t total = 0;
-    CUDA_TRY(ctx, cudaMemcpyAsync(&total, tile_off + n_tiles, 8, cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(ctx, cudaStreamSynchronize(s));
-    st = ctx_read_status(ctx, s);
-    if (st) return ctx_status_to_code(ctx, st);
-    *n_out = total;
-    if (total > cap) return ctx_fail(ctx, BPE_ERR_CAPACITY, "output buffer too small");
-    {
-        KernelTimer t(ctx, "emit_write_kernel", s);
-        if (out_elem_bytes == 2) emit_write_kernel<uint16_t><<<(unsigned)n_tiles, ENC_THREADS, 0, s>>>(P, ctx->sp, tile_off, chunk_cnt, (uint16_t*)d_out);
-        else emit_write_kernel<uint32_t><<<(unsigned)n_tiles, ENC_THREADS, 0, s>>>(P, ctx->sp, tile_off, chunk_cnt, (uint32_t*)d_out);
-        CUDA_TRY(ctx, cudaGetLastError());
-    }
-    CUDA_TRY(ctx, cudaStreamSynchronize(s));
-    return ctx_status_to_code(ctx, ctx_read_status(ctx, s));
+    return ctx_fail(ctx, BPE_ERR_STATE, "encode did not converge");
 }
 
 int run_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_ids, const uint8_t* h_vocab_blob,

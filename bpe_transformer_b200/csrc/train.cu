@@ -69,6 +69,8 @@ struct Ctrl {
     unsigned int n_hot;       // length of `hot`
     unsigned int n_rebuilds;
     unsigned int n_heavy;
+    unsigned int go;          // grid variant: heavy steps announced by the driver CTA (helpers poll it)
+    unsigned int done;        // grid variant: helper CTAs that finished their share, summed over all heavy steps
     unsigned int pad;
     Command cmd;
     unsigned int dbg[8];      // flags bit 1: [0] stale cache copies, [1] first iteration with one, [2] hot pairs missing from the cache, [3] first iteration
@@ -82,7 +84,7 @@ struct TrainState {
     unsigned long long* ph_key; long long* ph_cnt; uint32_t* live; ulonglong2* hot; uint64_t ph_mask;
     // tokens
     uint32_t* tk_off; uint8_t* tk_blob; uint32_t blob_cap; unsigned long long* tk_pre; uint32_t* wl_off; uint32_t* wl_len;
-    uint32_t* wl_pool; uint32_t wl_cap;
+    uint2* wl_pool; uint32_t wl_cap;  // postings: (word, offset of its symbols): one load less on the way to the symbols
     uint32_t* m_a; uint32_t* m_b;
     Ctrl* ctrl;
     uint32_t* trace;  // optional (BPE_B200_TRAIN_TRACE): per iteration {ns, list length, 1 = all words, matched}
@@ -264,10 +266,11 @@ __device__ __forceinline__ Best shfl_best(const Best& b, int o, bool down) {
 
 // ---- word rewriting -----------------------------------------------------------------------------------------------------
 // Does the word contain (a, b)?  One thread, 16-byte loads (independent of one another, so they overlap).
-__device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, uint32_t a, uint32_t b) {
-    const uint4* s4 = reinterpret_cast<const uint4*>(S.sym + S.w_off[w]);
+__device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, uint32_t off, uint32_t a, uint32_t b, uint32_t* len_out) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(S.sym + off);
     uint4 v = __ldcg(s4);                        // every word owns at least 4 symbol slots: load before the length is known
     const uint32_t len = __ldcg(S.w_len + w);
+    *len_out = len;
     if (len < 2) return false;
     bool hit = (v.x == a && v.y == b) | (2 < len && v.y == a && v.z == b) | (3 < len && v.z == a && v.w == b);
     uint32_t prev = v.w;
@@ -283,9 +286,8 @@ __device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, u
 // One word, one thread: replace (a, b) by x left to right without overlap, apply the reference's count deltas.
 // Returns whether anything matched.  (Words longer than a warp, and queue overflow.)
 template <class Adder>
-__device__ bool rewrite_word_serial(const TrainState& S, uint32_t w, uint32_t a, uint32_t b, uint32_t x, const Adder& add) {
-    uint32_t* s = S.sym + S.w_off[w];
-    uint32_t len = __ldcg(S.w_len + w);
+__device__ bool rewrite_word_serial(const TrainState& S, uint32_t w, uint32_t off, uint32_t len, uint32_t a, uint32_t b, uint32_t x, const Adder& add) {
+    uint32_t* s = S.sym + off;
     if (len < 2) return false;
     long long c = S.w_cnt[w];
     uint32_t m = 0, j = 0, hits = 0;
@@ -320,15 +322,14 @@ __device__ bool rewrite_word_serial(const TrainState& S, uint32_t w, uint32_t a,
 // (left neighbour in the new word, x) and (x, right neighbour in the new word), a neighbour being x itself when the
 // adjacent original positions were a match too.  Returns (warp-uniform) whether anything matched.
 template <class Adder>
-__device__ bool rewrite_word_warp(const TrainState& S, uint32_t w, uint32_t a, uint32_t b, uint32_t x, const Adder& add) {
+__device__ bool rewrite_word_warp(const TrainState& S, uint32_t w, uint32_t off, uint32_t len, uint32_t a, uint32_t b, uint32_t x, const Adder& add) {
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t len = __ldcg(S.w_len + w);
     if (len < 2) return false;
     if (len > 32) {
-        bool hit = lane == 0 ? rewrite_word_serial(S, w, a, b, x, add) : false;
+        bool hit = lane == 0 ? rewrite_word_serial(S, w, off, len, a, b, x, add) : false;
         return __shfl_sync(0xFFFFFFFFu, hit, 0);
     }
-    uint32_t* s = S.sym + S.w_off[w];
+    uint32_t* s = S.sym + off;
     const uint32_t me = lane < len ? __ldcg(s + lane) : NONE;
     const long long c = S.w_cnt[w];
     const uint32_t next1 = __shfl_down_sync(0xFFFFFFFFu, me, 1), prev1 = __shfl_up_sync(0xFFFFFFFFu, me, 1);
@@ -359,34 +360,40 @@ __device__ bool rewrite_word_warp(const TrainState& S, uint32_t w, uint32_t a, u
 
 // The candidates of a heavy step, spread over all CTAs: every thread filters one candidate word per round, the CTA's
 // warps rewrite the hits.  Rewritten words are appended to the posting pool through the global cursor.
+// Hits of the filter stage, handed from threads to warps through shared memory.
+struct Queue {
+    uint32_t w[QUEUE_CAP], off[QUEUE_CAP], len[QUEUE_CAP];
+    unsigned int n;
+};
+
 template <int NT>
-__device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t n_words, uint32_t* sh_queue, unsigned int* sh_qn) {
+__device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t n_words, Queue& Q) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gsize = gridDim.x * NT;
-    const uint32_t* list = cmd.list_tok == NONE ? nullptr : S.wl_pool + __ldcg(S.wl_off + cmd.list_tok);
+    const uint2* list = cmd.list_tok == NONE ? nullptr : S.wl_pool + __ldcg(S.wl_off + cmd.list_tok);
     const uint32_t n_cand = list ? cmd.list_len : n_words;
     const GlobalAdder add{S, cmd.threshold};
     for (uint32_t base = blockIdx.x * NT; base < n_cand; base += gsize) {
-        if (tid == 0) *sh_qn = 0;
+        if (tid == 0) Q.n = 0;
         __syncthreads();
         const uint32_t i = base + tid;
         if (i < n_cand) {
-            const uint32_t w = list ? __ldcg(list + i) : i;
-            if (word_has_pair(S, w, cmd.a, cmd.b)) {
-                unsigned int q = atomicAdd(sh_qn, 1u);
-                if (q < QUEUE_CAP) sh_queue[q] = w;
-                else if (rewrite_word_serial(S, w, cmd.a, cmd.b, cmd.x, add)) {
+            uint32_t w, off, len;
+            if (list) { const uint2 e = __ldcg(list + i); w = e.x; off = e.y; } else { w = i; off = S.w_off[i]; }
+            if (word_has_pair(S, w, off, cmd.a, cmd.b, &len)) {
+                unsigned int q = atomicAdd(&Q.n, 1u);
+                if (q < QUEUE_CAP) { Q.w[q] = w; Q.off[q] = off; Q.len[q] = len; }
+                else if (rewrite_word_serial(S, w, off, len, cmd.a, cmd.b, cmd.x, add)) {
                     unsigned int at = atomicAdd(&S.ctrl->wl_cursor, 1u);
-                    if (at < S.wl_cap) S.wl_pool[at] = w; else set_status(S.status, ST_LIST_FULL);
+                    if (at < S.wl_cap) S.wl_pool[at] = make_uint2(w, off); else set_status(S.status, ST_LIST_FULL);
                 }
             }
         }
         __syncthreads();
-        const uint32_t qn = min(*sh_qn, QUEUE_CAP);
+        const uint32_t qn = min(Q.n, QUEUE_CAP);
         for (uint32_t k = warp; k < qn; k += NT / 32) {
-            const uint32_t w = sh_queue[k];
-            if (rewrite_word_warp(S, w, cmd.a, cmd.b, cmd.x, add) && lane == 0) {
+            if (rewrite_word_warp(S, Q.w[k], Q.off[k], Q.len[k], cmd.a, cmd.b, cmd.x, add) && lane == 0) {
                 unsigned int at = atomicAdd(&S.ctrl->wl_cursor, 1u);
-                if (at < S.wl_cap) S.wl_pool[at] = w; else set_status(S.status, ST_LIST_FULL);
+                if (at < S.wl_cap) S.wl_pool[at] = make_uint2(Q.w[k], Q.off[k]); else set_status(S.status, ST_LIST_FULL);
             }
         }
         __syncthreads();
@@ -395,8 +402,46 @@ __device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t 
 
 template <bool CLUSTER, int NT>
 __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
-    auto sync_all = [] {
-        if constexpr (CLUSTER) cg::this_cluster().sync(); else cg::this_grid().sync();
+    // Driver <-> helper hand-over around a heavy step.  CLUSTER: the hardware cluster barrier on both sides.  Otherwise
+    // (a cooperative grid, one CTA per SM): helpers poll a counter in global memory, so the driver's light steps involve
+    // no barrier at all and a heavy step has all 148 SMs.
+    uint32_t seen = 0;  // helper: heavy steps seen so far; driver: heavy steps issued so far
+    auto helper_wait = [&] {
+        if constexpr (CLUSTER) cg::this_cluster().sync();
+        else {
+            if (threadIdx.x == 0) {
+                while (*reinterpret_cast<volatile unsigned int*>(&S.ctrl->go) == seen) __nanosleep(256);
+                __threadfence();
+            }
+            seen++;
+            __syncthreads();
+        }
+    };
+    auto helper_done = [&] {
+        if constexpr (CLUSTER) cg::this_cluster().sync();
+        else {
+            __syncthreads();
+            if (threadIdx.x == 0) { __threadfence(); atomicAdd(&S.ctrl->done, 1u); }
+        }
+    };
+    auto driver_wake = [&] {  // the command has been written by thread 0
+        if constexpr (CLUSTER) cg::this_cluster().sync();
+        else {
+            seen++;
+            if (threadIdx.x == 0) { __threadfence(); atomicAdd(&S.ctrl->go, 1u); }
+        }
+    };
+    auto driver_join = [&] {
+        if constexpr (CLUSTER) cg::this_cluster().sync();
+        else {
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const unsigned int want = seen * (gridDim.x - 1);
+                while (*reinterpret_cast<volatile unsigned int*>(&S.ctrl->done) < want) {}
+                __threadfence();
+            }
+            __syncthreads();
+        }
     };
     extern __shared__ __align__(16) unsigned char smem_raw[];
     HotCache& H = *reinterpret_cast<HotCache*>(smem_raw);  // used by the driver CTA only
@@ -405,8 +450,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
     __shared__ unsigned int sh_ntie;
     __shared__ Best sh_win;
     __shared__ Best sh_bestw[NT / 32];
-    __shared__ uint32_t sh_queue[QUEUE_CAP];
-    __shared__ unsigned int sh_qn;
+    __shared__ Queue Q;
     __shared__ unsigned int sh_hist[64];
     __shared__ unsigned int sh_sub[SUB_BINS];
     __shared__ long long sh_T;
@@ -419,10 +463,10 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
 
     if (blockIdx.x != 0) {  // helper CTAs: asleep on the barrier until the driver broadcasts a heavy step
         for (uint32_t round = 0;; round++) {
-            if (tid == 0) { S.beat[2 * blockIdx.x] = round; S.beat[2 * blockIdx.x + 1] = 20; }
-            sync_all();
+            if (tid == 0 && blockIdx.x < 16) { S.beat[2 * blockIdx.x] = round; S.beat[2 * blockIdx.x + 1] = 20; }
+            helper_wait();
             if (tid == 0) {
-                S.beat[2 * blockIdx.x + 1] = 21;
+                if (blockIdx.x < 16) S.beat[2 * blockIdx.x + 1] = 21;
                 const volatile Command* c = &S.ctrl->cmd;
                 sh_cmd.op = c->op; sh_cmd.a = c->a; sh_cmd.b = c->b; sh_cmd.x = c->x; sh_cmd.list_tok = c->list_tok;
                 sh_cmd.list_len = c->list_len; sh_cmd.threshold = c->threshold;
@@ -430,9 +474,9 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             __syncthreads();
             const Command cmd = sh_cmd;
             if (cmd.op == 0) return;
-            heavy_rewrite<NT>(S, cmd, n_words, sh_queue, &sh_qn);
-            if (tid == 0) S.beat[2 * blockIdx.x + 1] = 22;
-            sync_all();
+            heavy_rewrite<NT>(S, cmd, n_words, Q);
+            if (tid == 0 && blockIdx.x < 16) S.beat[2 * blockIdx.x + 1] = 22;
+            helper_done();
         }
     }
 
@@ -624,17 +668,18 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         const uint32_t a = (uint32_t)((win.key - 1) >> 32), b = (uint32_t)(win.key - 1), x = next_id;
 
         // ---- the words that can contain (a, b): the shorter posting list of the two tokens, all words for two bytes ------
-        uint32_t list_tok = NONE, list_len = n_words;
-        if (a >= S.first_new_id) { list_tok = a; list_len = __ldcg(S.wl_len + a); }
-        if (b >= S.first_new_id) {
-            uint32_t lb = __ldcg(S.wl_len + b);
-            if (list_tok == NONE || lb < list_len) { list_tok = b; list_len = lb; }
+        uint32_t list_tok = NONE, list_len = n_words, list_off = 0;
+        {   // both tokens' posting heads in one round trip
+            const bool ma = a >= S.first_new_id, mb = b >= S.first_new_id;
+            const uint32_t la = ma ? __ldcg(S.wl_len + a) : 0, oa = ma ? __ldcg(S.wl_off + a) : 0;
+            const uint32_t lb = mb ? __ldcg(S.wl_len + b) : 0, ob = mb ? __ldcg(S.wl_off + b) : 0;
+            if (ma) { list_tok = a; list_len = la; list_off = oa; }
+            if (mb && (!ma || lb < la)) { list_tok = b; list_len = lb; list_off = ob; }
         }
-        if (tid == 0) S.beat[1] = 3;
         const uint32_t wl_start = wl_cur;
         const uint32_t first_new_entry = n_cached;
         uint32_t matched = 0;
-        if (tid == 0) sh_qn = 0;
+        if (tid == 0) Q.n = 0;
         if (leader) {  // bookkeeping for x beside the rewrite (speculative: overwritten if the step merges nothing)
             const uint32_t oa = __ldcg(S.tk_off + a), ob = __ldcg(S.tk_off + b), o = __ldcg(S.tk_off + x);
             const uint32_t la = __ldcg(S.tk_off + a + 1) - oa, lb = __ldcg(S.tk_off + b + 1) - ob;
@@ -654,25 +699,29 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         if (tracer) c2 = clock64();
         if (list_tok != NONE && list_len <= LIGHT_MAX) {
             // light step, this CTA alone: filter (one thread per posting), then one warp per hit
-            const uint32_t* list = S.wl_pool + __ldcg(S.wl_off + list_tok);
-            __syncthreads();  // sh_qn = 0
+            const uint2* list = S.wl_pool + list_off;
+            __syncthreads();  // Q.n = 0
             for (uint32_t i = tid; i < list_len; i += NT) {
-                const uint32_t w = __ldcg(list + i);
-                if (word_has_pair(S, w, a, b)) sh_queue[atomicAdd(&sh_qn, 1u)] = w;  // list_len <= QUEUE_CAP
+                const uint2 e = __ldcg(list + i);
+                uint32_t len;
+                if (word_has_pair(S, e.x, e.y, a, b, &len)) {  // list_len <= QUEUE_CAP
+                    const unsigned int q = atomicAdd(&Q.n, 1u);
+                    Q.w[q] = e.x; Q.off[q] = e.y; Q.len[q] = len;
+                }
             }
             __syncthreads();
-            matched = sh_qn;
+            matched = Q.n;
             if (tid == 0) S.beat[1] = 5;
             if (tracer) c3 = clock64();
             if (use_cache) {
                 const CacheAdder add{S, H, T};
-                for (uint32_t k = warp; k < matched; k += NT / 32) rewrite_word_warp(S, sh_queue[k], a, b, x, add);
+                for (uint32_t k = warp; k < matched; k += NT / 32) rewrite_word_warp(S, Q.w[k], Q.off[k], Q.len[k], a, b, x, add);
             } else {
                 const GlobalAdder add{S, LLONG_MAX};
-                for (uint32_t k = warp; k < matched; k += NT / 32) rewrite_word_warp(S, sh_queue[k], a, b, x, add);
+                for (uint32_t k = warp; k < matched; k += NT / 32) rewrite_word_warp(S, Q.w[k], Q.off[k], Q.len[k], a, b, x, add);
             }
             for (uint32_t k = tid; k < matched; k += NT) {  // the hits ARE x's posting list
-                if (wl_start + k < S.wl_cap) S.wl_pool[wl_start + k] = sh_queue[k]; else set_status(S.status, ST_LIST_FULL);
+                if (wl_start + k < S.wl_cap) S.wl_pool[wl_start + k] = make_uint2(Q.w[k], Q.off[k]); else set_status(S.status, ST_LIST_FULL);
             }
             if (tid == 0) S.beat[1] = 6;
             __threadfence();  // the count updates were posted without waiting: they must have landed before the reload below
@@ -690,13 +739,13 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
                 __threadfence();
                 S.beat[1] = 7;
             }
-            sync_all();
+            driver_wake();
             if (tid == 0) S.beat[1] = 8;
             if (tracer) c3 = clock64();
             const Command cmd{1u, a, b, x, list_tok, list_len, T};
-            heavy_rewrite<NT>(S, cmd, n_words, sh_queue, &sh_qn);
+            heavy_rewrite<NT>(S, cmd, n_words, Q);
             if (tid == 0) S.beat[1] = 9;
-            sync_all();
+            driver_join();
             if (tid == 0) S.beat[1] = 10;
             matched = __ldcg(&S.ctrl->wl_cursor) - wl_start;
             for (uint32_t i = tid; i < n_cached; i += NT)
@@ -747,7 +796,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         __threadfence();
         S.beat[1] = 12;
     }
-    sync_all();  // releases the helpers, which read op = 0 and leave
+    driver_wake();  // releases the helpers, which read op = 0 and leave
 }
 
 size_t next_pow2(size_t v) { size_t p = 1; while (p < v) p <<= 1; return p; }
@@ -783,7 +832,7 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
         {(void**)&S.sym, (n_sym + 4 * n_unique + 8) * 4},
         {(void**)&S.ph_key, ph_cap * 8}, {(void**)&S.ph_cnt, ph_cap * 8}, {(void**)&S.live, ph_cap * 4}, {(void**)&S.hot, (ph_cap + 1) * 16},
         {(void**)&S.tk_off, (vocab_size + 2) * 4ull}, {(void**)&S.tk_blob, S.blob_cap}, {(void**)&S.tk_pre, (vocab_size + 1) * 8ull},
-        {(void**)&S.wl_off, (vocab_size + 1) * 4ull}, {(void**)&S.wl_len, (vocab_size + 1) * 4ull}, {(void**)&S.wl_pool, (size_t)S.wl_cap * 4},
+        {(void**)&S.wl_off, (vocab_size + 1) * 4ull}, {(void**)&S.wl_len, (vocab_size + 1) * 4ull}, {(void**)&S.wl_pool, (size_t)S.wl_cap * 8},
         {(void**)&S.m_a, (vocab_size + 1) * 4ull}, {(void**)&S.m_b, (vocab_size + 1) * 4ull},
         {(void**)&S.ctrl, sizeof(Ctrl)}, {(void**)&S.trace, (vocab_size + 1) * 16ull},
     };
@@ -847,11 +896,11 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     CUDA_TRY(ctx, cudaHostGetDevicePointer((void**)&d_beat, h_beat, 0));
     S.beat = d_beat;
     int launched_ctas = 0;
-    // One cluster with the hardware barrier while the word table is small enough to be swept by ~16k threads in a few
-    // microseconds; a cooperative grid beyond that.
+    // Default: a cooperative grid, one CTA per SM, helpers polling a flag (measured faster than the one-cluster variant:
+    // heavy steps get all SMs).  BPE_B200_TRAIN_MODE=cluster selects the single-cluster variant (experiments, tests).
     bool launched = false;
-    const char* mode = getenv("BPE_B200_TRAIN_MODE");  // "grid" / "cluster" force a variant (experiments, tests)
-    if (!(mode && !strcmp(mode, "grid")) && (n_words <= (4u << 20) || (mode && !strcmp(mode, "cluster")))) {
+    const char* mode = getenv("BPE_B200_TRAIN_MODE");
+    if (mode && !strcmp(mode, "cluster")) {
         auto kern = merge_loop_kernel<true, 1024>;
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HotCache));
@@ -869,21 +918,23 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
         }
     }
     if (!launched) {
-        auto kern = merge_loop_kernel<false, 512>;
+        int nt = 512;
+        if (const char* env = getenv("BPE_B200_TRAIN_NT")) nt = atoi(env);
+        void (*kern)(TrainState) = nt == 1024 ? merge_loop_kernel<false, 1024> : nt == 256 ? merge_loop_kernel<false, 256> : merge_loop_kernel<false, 512>;
+        if (nt != 1024 && nt != 256) nt = 512;
         int per_sm = 0;
         CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HotCache)));
-        CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 512, sizeof(HotCache)));
+        CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt, sizeof(HotCache)));
         cudaDeviceProp prop;
         CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, ctx->device));
-        int grid = prop.multiProcessorCount * (per_sm > 1 ? 1 : per_sm);
-        grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((n_words + 511) / 512, (uint64_t)grid));
+        int grid = per_sm >= 1 ? prop.multiProcessorCount : 1;  // helpers poll a flag: every CTA must be resident (cooperative launch)
         if (const char* env = getenv("BPE_B200_TRAIN_CTAS")) {
             int v = atoi(env);
-            if (v >= 1 && v <= prop.multiProcessorCount * per_sm) grid = v;
+            if (v >= 1 && v <= grid) grid = v;
         }
         KernelTimer t(ctx, "merge_loop_kernel", s);
         void* args[] = {&S};
-        CUDA_TRY(ctx, cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(512), args, sizeof(HotCache), s));
+        CUDA_TRY(ctx, cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(nt), args, sizeof(HotCache), s));
         launched_ctas = grid;
     }
     {   // wait with a deadline

@@ -112,7 +112,9 @@ def count_shard(engine: "_lib.Engine", path, lo: int, hi: int, special_tokens: l
             clean, _ = _sanitised(fh.read(hi - lo), [], strict=False)
         d_text, n = engine.to_device(clean)
         mask = engine.scan(d_text, n)
-    engine.count(d_text, n, mask)
+    from .tokenization.preprocessing.pretokenization import count_with_growth
+
+    count_with_growth(engine, d_text, n, mask, keep_counted=not reset)
     return d_text, n
 
 

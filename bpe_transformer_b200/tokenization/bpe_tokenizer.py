@@ -106,14 +106,16 @@ class BPETokenizer(Tokenizer):
         """UTF-8 bytes (bytes / pinned uint8 tensor) -> device tensor of ids (uint16 bit pattern in int16, or int32).
         `on_device` = (padded device tensor, length) skips the upload."""
         engine = engine or _lib.get_engine()
-        wide = self._bind(engine)
         d_text, n = on_device if on_device is not None else engine.to_device(data)
-        try:
-            return engine.encode(d_text, n, cuts=cuts, flags=flags, wide=wide)
-        except _lib.BpeError as e:
-            if e.code == _lib.ERR_MISSING_ID:  # bpe_tokenizer.py:175, :206, :290
-                raise KeyError("bytes without an id in the vocabulary") from e
-            raise
+        while True:
+            wide = self._bind(engine)
+            try:
+                return engine.encode(d_text, n, cuts=cuts, flags=flags, wide=wide)
+            except _lib.BpeError as e:
+                if e.code == _lib.ERR_MISSING_ID:  # bpe_tokenizer.py:175, :206, :290
+                    raise KeyError("bytes without an id in the vocabulary") from e
+                if e.code != _lib.ERR_CAPACITY or not engine.grow():  # more distinct pretokens than the cache holds: enlarge it
+                    raise
 
     @staticmethod
     def _ids_to_numpy(ids) -> np.ndarray:

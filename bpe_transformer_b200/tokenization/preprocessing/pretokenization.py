@@ -135,7 +135,19 @@ def count_into_engine(engine: "_lib.Engine", file_path, special_tokens: list[str
             clean, cuts = _sanitised(fh.read(), cuts, strict)
         d_text, n = engine.to_device(clean)
         mask = engine.scan(d_text, n, cuts=cuts)
-    engine.count(d_text, n, mask)
+    count_with_growth(engine, d_text, n, mask)
+
+
+def count_with_growth(engine: "_lib.Engine", d_text, n: int, mask, keep_counted: bool = False) -> None:
+    """bpe_count; if the context's table of distinct pretokens or its byte pool is too small for this corpus, enlarge
+    it (x4) and count again.  `keep_counted`: earlier shards are in the table and must not be dropped -> no retry."""
+    while True:
+        try:
+            engine.count(d_text, n, mask)
+            return
+        except _lib.BpeError as e:
+            if e.code != _lib.ERR_CAPACITY or keep_counted or not engine.grow():
+                raise
 
 
 def counter_from_engine(engine: "_lib.Engine") -> Counter:

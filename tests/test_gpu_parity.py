@@ -337,6 +337,39 @@ def test_encode_error_conventions(gpt2_model):
     assert get_tokenizer(dict(vocab), merges, None).decode([0, 10**9, 1]) == port.PortTokenizer(vocab, merges).decode([0, 10**9, 1])
 
 
+def test_encode_dense_windows_and_warm_cache(gpt2_model):
+    """Windows of 1 KiB with more tokens than the emit pass keeps on chip (one-byte tokens), and texts that bring
+    new pretokens to a cache that earlier calls have filled: same ids as the oracle, call after call."""
+    from adapters import get_tokenizer
+
+    vocab, merges = gpt2_model
+    vocab = with_specials(vocab, [EOT])
+    tok = get_tokenizer(vocab, merges, [EOT])
+    ct = c_oracle.COracleTokenizer(vocab, merges, [EOT])
+    rng = np.random.default_rng(7)
+    dense = "".join(rng.choice(list("a.b,c;d!e?f:g(h)1-2+"), size=40_000).tolist())
+    words = " ".join("w%d" % v for v in rng.integers(0, 5000, size=20_000))
+    later = " ".join("later%dx" % v for v in rng.integers(0, 3000, size=10_000)) + EOT + dense[:5000]
+    for text in (dense, words, dense + EOT + words, later, dense, later + "\n" + words):
+        assert tok.encode(text) == ct.encode(text)
+    long_ids = "z" * 3000 + " " + "ab" * 2000  # two pretokens with hundreds of ids each
+    assert tok.encode(long_ids) == ct.encode(long_ids)
+
+
+def test_encode_keyerror_is_raised_every_time(gpt2_model):
+    """A pretoken that cannot be encoded is not cached as if it had been: the reference raises on every call."""
+    from adapters import get_tokenizer
+
+    vocab, merges = gpt2_model
+    small = {k: v for k, v in vocab.items() if v != b"z"}
+    tok = get_tokenizer(small, merges, None)
+    fine = tok.encode("a plain sentence")
+    for _ in range(3):
+        with pytest.raises(KeyError):
+            tok.encode("a plain zebra sentence")
+        assert tok.encode("a plain sentence") == fine
+
+
 def test_model_and_dataset_formats(tmp_path, gpt2_model, input_bytes, tmp_file):
     """GPT-2 text formats round trip; a tokenized file lands in a .npy that holds encode_iterable's ids."""
     from adapters import get_tokenizer
