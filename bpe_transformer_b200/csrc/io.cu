@@ -3,12 +3,14 @@
 //
 // The reference reads its corpus with f.read() per worker (pretokenization.py:192-194); here the whole byte range goes to
 // one device buffer.  Reading 2 GB through a single thread (~5 GB/s from the page cache) and pinning 2 GB of fresh host
-// memory per call cost more than every kernel together, hence: a few persistent pinned buffers per context, a handful of
-// reader threads per chunk, cudaMemcpyAsync per chunk on a copy stream.
+// memory per call cost more than every kernel together, hence: persistent pinned buffers per context and up to 16 host
+// threads ("lanes"), each reading 4 MB chunks into its own pair of buffers and copying them on its own stream.
 #include <fcntl.h>
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -17,69 +19,70 @@
 
 namespace {
 
-constexpr int kStageBuffers = 3;
-constexpr size_t kStageBytes = 32u << 20;
+// Every lane is one host thread with its own copy stream and two pinned buffers: while the DMA engine drains one buffer the
+// thread fills (or empties) the other.  Lanes take chunks off a shared counter and never wait for one another.
+constexpr int kMaxLanes = 16;
+constexpr size_t kLaneBytes = 4u << 20;
 
 struct Staging {
-    uint8_t* buf[kStageBuffers] = {nullptr, nullptr, nullptr};
-    cudaEvent_t done[kStageBuffers] = {nullptr, nullptr, nullptr};
-    cudaStream_t copy = nullptr;
+    int lanes = 0;
+    uint8_t* block = nullptr;  // lanes * 2 * kLaneBytes of pinned memory
+    cudaStream_t copy[kMaxLanes] = {};
+    cudaEvent_t done[kMaxLanes][2] = {};
+    uint8_t* buf(int lane, int b) const { return block + ((size_t)lane * 2 + b) * kLaneBytes; }
 };
+
+int n_io_lanes() {
+    if (const char* e = getenv("BPE_B200_IO_THREADS")) {
+        int v = atoi(e);
+        if (v >= 1) return std::min(v, kMaxLanes);
+    }
+    unsigned hw = std::thread::hardware_concurrency();
+    if (!hw) hw = 4;
+    unsigned share = 1;  // processes of this node that load at the same time (one per GPU under torchrun)
+    if (const char* e = getenv("LOCAL_WORLD_SIZE")) { int v = atoi(e); if (v > 1) share = (unsigned)v; }
+    return (int)std::max(2u, std::min((unsigned)kMaxLanes, hw / share));
+}
 
 Staging* staging_of(bpe_ctx* ctx) {
     if (ctx->io_staging) return static_cast<Staging*>(ctx->io_staging);
     Staging* st = new Staging();
-    bool ok = cudaStreamCreateWithFlags(&st->copy, cudaStreamNonBlocking) == cudaSuccess;
-    for (int k = 0; ok && k < kStageBuffers; k++)
-        ok = cudaHostAlloc((void**)&st->buf[k], kStageBytes, cudaHostAllocDefault) == cudaSuccess &&
-             cudaEventCreateWithFlags(&st->done[k], cudaEventDisableTiming) == cudaSuccess;
+    st->lanes = n_io_lanes();
+    bool ok = cudaHostAlloc((void**)&st->block, (size_t)st->lanes * 2 * kLaneBytes, cudaHostAllocDefault) == cudaSuccess;
+    for (int l = 0; ok && l < st->lanes; l++)
+        ok = cudaStreamCreateWithFlags(&st->copy[l], cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreateWithFlags(&st->done[l][0], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&st->done[l][1], cudaEventDisableTiming) == cudaSuccess;
+    ctx->io_staging = st;
     if (!ok) {
         ctx_fail(ctx, BPE_ERR_CUDA, "allocating pinned staging buffers", cudaGetLastError());
-        delete st;
+        io_staging_free(ctx);
         return nullptr;
     }
-    ctx->io_staging = st;
     return st;
 }
 
-int n_io_threads() {
-    unsigned hw = std::thread::hardware_concurrency();
-    return (int)std::max(1u, std::min(8u, hw ? hw : 4u));
-}
-
-// Fills dst[0, n) from the file at offset `off` with several threads; returns false on a short read.
-bool parallel_pread(int fd, uint8_t* dst, size_t n, uint64_t off) {
-    const int T = n < (4u << 20) ? 1 : n_io_threads();
-    std::vector<std::thread> th;
-    std::vector<int> bad(T, 0);
-    const size_t per = (n + T - 1) / T;
-    for (int t = 0; t < T; t++) {
-        const size_t a = std::min(n, t * per), b = std::min(n, a + per);
-        auto work = [fd, dst, off, a, b, &bad, t] {
-            size_t got = a;
-            while (got < b) {
-                ssize_t k = pread(fd, dst + got, b - got, (off_t)(off + got));
-                if (k <= 0) { bad[t] = 1; return; }
-                got += (size_t)k;
-            }
-        };
-        if (t + 1 == T) work(); else th.emplace_back(work);
+bool pread_all(int fd, uint8_t* dst, size_t n, uint64_t off) {
+    size_t got = 0;
+    while (got < n) {
+        ssize_t k = pread(fd, dst + got, n - got, (off_t)(off + got));
+        if (k <= 0) return false;
+        got += (size_t)k;
     }
-    for (auto& x : th) x.join();
-    for (int v : bad) if (v) return false;
     return true;
 }
 
-void parallel_memcpy(uint8_t* dst, const uint8_t* src, size_t n) {
-    const int T = n < (4u << 20) ? 1 : n_io_threads();
+// Runs work(lane) on st->lanes threads (fewer for small jobs); returns the first non-zero result.
+template <class F>
+int run_lanes(const Staging* st, uint64_t n_chunks, F work) {
+    const int T = (int)std::min<uint64_t>((uint64_t)st->lanes, std::max<uint64_t>(1, n_chunks));
+    std::vector<int> rc(T, 0);
     std::vector<std::thread> th;
-    const size_t per = (n + T - 1) / T;
-    for (int t = 0; t < T; t++) {
-        const size_t a = std::min(n, t * per), b = std::min(n, a + per);
-        auto work = [dst, src, a, b] { memcpy(dst + a, src + a, b - a); };
-        if (t + 1 == T) work(); else th.emplace_back(work);
-    }
+    for (int l = 1; l < T; l++) th.emplace_back([&rc, &work, l] { rc[l] = work(l); });
+    rc[0] = work(0);
     for (auto& x : th) x.join();
+    for (int v : rc) if (v) return v;
+    return 0;
 }
 
 }  // namespace
@@ -87,15 +90,16 @@ void parallel_memcpy(uint8_t* dst, const uint8_t* src, size_t n) {
 void io_staging_free(bpe_ctx* ctx) {
     if (!ctx->io_staging) return;
     Staging* st = static_cast<Staging*>(ctx->io_staging);
-    for (int k = 0; k < kStageBuffers; k++) {
-        if (st->buf[k]) cudaFreeHost(st->buf[k]);
-        if (st->done[k]) cudaEventDestroy(st->done[k]);
+    for (int l = 0; l < kMaxLanes; l++) {
+        if (st->copy[l]) cudaStreamDestroy(st->copy[l]);
+        for (int b = 0; b < 2; b++) if (st->done[l][b]) cudaEventDestroy(st->done[l][b]);
     }
-    if (st->copy) cudaStreamDestroy(st->copy);
+    if (st->block) cudaFreeHost(st->block);
     delete st;
     ctx->io_staging = nullptr;
 }
 
+// Lane results: 1 = short read, 2 = CUDA error.
 extern "C" int bpe_load_file(bpe_ctx* ctx, const char* path, uint64_t offset, uint64_t n, uint8_t* d_dst, void* stream) {
     if (!ctx || !path || (n && !d_dst)) return ctx ? ctx_fail(ctx, BPE_ERR_ARGUMENT, "bpe_load_file arguments") : BPE_ERR_ARGUMENT;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -104,22 +108,30 @@ extern "C" int bpe_load_file(bpe_ctx* ctx, const char* path, uint64_t offset, ui
     if (!st) return BPE_ERR_CUDA;
     int fd = open(path, O_RDONLY);
     if (fd < 0) return ctx_fail(ctx, BPE_ERR_ARGUMENT, "cannot open file");
-    int rc = BPE_OK;
-    uint64_t done = 0;
-    for (int i = 0; done < n; i++) {
-        const int b = i % kStageBuffers;
-        const size_t len = (size_t)std::min<uint64_t>(kStageBytes, n - done);
-        if (i >= kStageBuffers && cudaEventSynchronize(st->done[b]) != cudaSuccess) { rc = ctx_fail(ctx, BPE_ERR_CUDA, "staging event", cudaGetLastError()); break; }
-        if (!parallel_pread(fd, st->buf[b], len, offset + done)) { rc = ctx_fail(ctx, BPE_ERR_ARGUMENT, "short read"); break; }
-        if (cudaMemcpyAsync(d_dst + done, st->buf[b], len, cudaMemcpyHostToDevice, st->copy) != cudaSuccess ||
-            cudaEventRecord(st->done[b], st->copy) != cudaSuccess) { rc = ctx_fail(ctx, BPE_ERR_CUDA, "host-to-device copy", cudaGetLastError()); break; }
-        done += len;
-    }
+    const uint64_t n_chunks = (n + kLaneBytes - 1) / kLaneBytes;
+    std::atomic<uint64_t> next{0};
+    const int device = ctx->device;
+    int rc = run_lanes(st, n_chunks, [&](int lane) -> int {
+        if (cudaSetDevice(device) != cudaSuccess) return 2;
+        int bad = 0;
+        for (int it = 0;; it++) {
+            const uint64_t c = next.fetch_add(1);
+            if (c >= n_chunks) break;
+            const int b = it & 1;
+            const size_t len = (size_t)std::min<uint64_t>(kLaneBytes, n - c * kLaneBytes);
+            if (it >= 2 && cudaEventSynchronize(st->done[lane][b]) != cudaSuccess) { bad = 2; break; }
+            if (!pread_all(fd, st->buf(lane, b), len, offset + c * kLaneBytes)) { bad = 1; break; }
+            if (cudaMemcpyAsync(d_dst + c * kLaneBytes, st->buf(lane, b), len, cudaMemcpyHostToDevice, st->copy[lane]) != cudaSuccess ||
+                cudaEventRecord(st->done[lane][b], st->copy[lane]) != cudaSuccess) { bad = 2; break; }
+        }
+        if (cudaStreamSynchronize(st->copy[lane]) != cudaSuccess && !bad) bad = 2;
+        return bad;
+    });
     close(fd);
-    cudaError_t e = cudaStreamSynchronize(st->copy);
-    if (rc == BPE_OK && e != cudaSuccess) rc = ctx_fail(ctx, BPE_ERR_CUDA, "host-to-device copy", e);
     (void)stream;  // the copy has completed on return: any stream may read the buffer afterwards
-    return rc;
+    if (rc == 1) return ctx_fail(ctx, BPE_ERR_ARGUMENT, "short read");
+    if (rc) return ctx_fail(ctx, BPE_ERR_CUDA, "host-to-device copy", cudaGetLastError());
+    return BPE_OK;
 }
 
 extern "C" int bpe_store_to_host(bpe_ctx* ctx, const void* d_src, uint64_t n, void* h_dst, void* stream) {
@@ -131,23 +143,32 @@ extern "C" int bpe_store_to_host(bpe_ctx* ctx, const void* d_src, uint64_t n, vo
     CUDA_TRY(ctx, cudaStreamSynchronize((cudaStream_t)stream));  // the producer of d_src has finished
     const uint8_t* src = static_cast<const uint8_t*>(d_src);
     uint8_t* dst = static_cast<uint8_t*>(h_dst);
-    const uint64_t n_chunks = (n + kStageBytes - 1) / kStageBytes;
-    // chunk i is copied to staging buffer i % K; it is drained to the destination while chunk i + 1 .. i + K - 1 are in flight
-    for (uint64_t i = 0; i < n_chunks + kStageBuffers - 1; i++) {
-        if (i >= (uint64_t)(kStageBuffers - 1)) {
-            const uint64_t j = i - (kStageBuffers - 1);  // drain chunk j
-            if (j < n_chunks) {
-                const int b = (int)(j % kStageBuffers);
-                CUDA_TRY(ctx, cudaEventSynchronize(st->done[b]));
-                parallel_memcpy(dst + j * kStageBytes, st->buf[b], (size_t)std::min<uint64_t>(kStageBytes, n - j * kStageBytes));
+    const uint64_t n_chunks = (n + kLaneBytes - 1) / kLaneBytes;
+    std::atomic<uint64_t> next{0};
+    const int device = ctx->device;
+    int rc = run_lanes(st, n_chunks, [&](int lane) -> int {
+        if (cudaSetDevice(device) != cudaSuccess) return 2;
+        // the chunk copied in round it is moved to the destination in round it + 1, while the next chunk is in flight
+        uint64_t prev_chunk = ~0ull;
+        size_t prev_len = 0;
+        for (int it = 0;; it++) {
+            const uint64_t c = next.fetch_add(1);
+            const int b = it & 1;
+            if (c < n_chunks) {
+                const size_t len = (size_t)std::min<uint64_t>(kLaneBytes, n - c * kLaneBytes);
+                if (cudaMemcpyAsync(st->buf(lane, b), src + c * kLaneBytes, len, cudaMemcpyDeviceToHost, st->copy[lane]) != cudaSuccess ||
+                    cudaEventRecord(st->done[lane][b], st->copy[lane]) != cudaSuccess) return 2;
             }
+            if (prev_chunk != ~0ull) {
+                if (cudaEventSynchronize(st->done[lane][b ^ 1]) != cudaSuccess) return 2;
+                memcpy(dst + prev_chunk * kLaneBytes, st->buf(lane, b ^ 1), prev_len);
+            }
+            if (c >= n_chunks) break;
+            prev_chunk = c;
+            prev_len = (size_t)std::min<uint64_t>(kLaneBytes, n - c * kLaneBytes);
         }
-        if (i < n_chunks) {
-            const int b = (int)(i % kStageBuffers);
-            const size_t len = (size_t)std::min<uint64_t>(kStageBytes, n - i * kStageBytes);
-            CUDA_TRY(ctx, cudaMemcpyAsync(st->buf[b], src + i * kStageBytes, len, cudaMemcpyDeviceToHost, st->copy));
-            CUDA_TRY(ctx, cudaEventRecord(st->done[b], st->copy));
-        }
-    }
+        return 0;
+    });
+    if (rc) return ctx_fail(ctx, BPE_ERR_CUDA, "device-to-host copy", cudaGetLastError());
     return BPE_OK;
 }
