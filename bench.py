@@ -40,7 +40,8 @@ METRIC = "train_bpe_seconds_10k_vocab_2.1GB"
 
 
 def log(*a):
-    print(*a, file=sys.stderr, flush=True)
+    if int(os.environ.get("RANK", "0")) == 0:  # one copy of every progress line under torchrun
+        print(*a, file=sys.stderr, flush=True)
 
 
 def corpus_path(nbytes: int, seed: int = 0) -> str:

@@ -200,10 +200,18 @@ class Engine:
     def to_host_array(self, d_tensor, dtype) -> np.ndarray:
         """Device tensor -> new NumPy array of `dtype` (same bytes), through the pinned staging buffers."""
         nbytes = int(d_tensor.numel()) * d_tensor.element_size()
-        out = np.empty(nbytes // np.dtype(dtype).itemsize, dtype=dtype)
+        out = host_array(nbytes // np.dtype(dtype).itemsize, dtype)
         if nbytes:
             self._check(self.lib.bpe_store_to_host(self.ctx, d_tensor.data_ptr(), nbytes, out.ctypes.data_as(C.c_void_p), self._stream()))
         return out
+
+    def store_into(self, d_tensor, out: np.ndarray) -> None:
+        """Device tensor -> an existing contiguous NumPy array of the same byte size."""
+        nbytes = int(d_tensor.numel()) * d_tensor.element_size()
+        if nbytes != out.nbytes or not out.flags.c_contiguous:
+            raise ValueError("store_into: size or layout mismatch")
+        if nbytes:
+            self._check(self.lib.bpe_store_to_host(self.ctx, d_tensor.data_ptr(), nbytes, out.ctypes.data_as(C.c_void_p), self._stream()))
 
     def new_mask(self, n: int):
         return self.torch.empty(n // 32 + 2, dtype=self.torch.int32, device=f"cuda:{self.device}")
@@ -316,6 +324,12 @@ class Engine:
         out = torch.empty(n_bytes.value + 16, dtype=torch.uint8, device=f"cuda:{self.device}")
         self._check(self.lib.bpe_decode(*args, out.data_ptr(), n_bytes.value, C.byref(n_bytes), self._stream()))
         return out[:n_bytes.value]
+
+
+def host_array(n_items: int, dtype) -> np.ndarray:
+    """Uninitialised NumPy array for results copied back from the GPU.  (Transparent huge pages were tried for the large
+    ones and made the first touch by 16 copy threads five times slower on the test box: plain pages it is.)"""
+    return np.empty(n_items, dtype=dtype)
 
 
 _engines: dict[int, Engine] = {}

@@ -4,11 +4,15 @@
 #include <cstring>
 
 #include "../../include/bpe_unicode_tables.h"
+#include <mutex>
+
 #include "common.cuh"
 
 static std::string g_create_error;
 
 int ctx_fail(bpe_ctx* ctx, int code, const char* what, cudaError_t e) {
+    static std::mutex mu;  // bpe_load_file / bpe_store_to_host may run beside another call on the same context
+    std::lock_guard<std::mutex> lock(mu);
     std::string msg = what ? what : "";
     if (e != cudaSuccess) { msg += ": "; msg += cudaGetErrorString(e); }
     if (ctx) ctx->err = msg; else g_create_error = msg;

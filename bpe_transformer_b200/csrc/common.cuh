@@ -275,7 +275,7 @@ struct bpe_ctx {
     // scratch reused across calls
     void* scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    void* io_staging = nullptr;  // io.cu: pinned staging buffers + copy stream
+    void* io_staging[2] = {nullptr, nullptr};  // io.cu: pinned staging buffers + copy streams; [0] loads, [1] stores (they may overlap)
     // timing
     bool profiling = false;
     std::vector<bpe_kernel_time> times;

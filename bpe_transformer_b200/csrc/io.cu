@@ -4,12 +4,15 @@
 // The reference reads its corpus with f.read() per worker (pretokenization.py:192-194); here the whole byte range goes to
 // one device buffer.  Reading 2 GB through a single thread (~5 GB/s from the page cache) and pinning 2 GB of fresh host
 // memory per call cost more than every kernel together, hence: persistent pinned buffers per context and up to 16 host
-// threads ("lanes"), each reading 4 MB chunks into its own pair of buffers and copying them on its own stream.
+// threads ("lanes"), each reading 2 MB chunks into its own pair of buffers and copying them on its own stream.
 #include <fcntl.h>
 #include <unistd.h>
 
 #include <algorithm>
 #include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <cstdlib>
 #include <cstring>
 #include <thread>
@@ -22,14 +25,66 @@ namespace {
 // Every lane is one host thread with its own copy stream and two pinned buffers: while the DMA engine drains one buffer the
 // thread fills (or empties) the other.  Lanes take chunks off a shared counter and never wait for one another.
 constexpr int kMaxLanes = 16;
-constexpr size_t kLaneBytes = 4u << 20;
+constexpr size_t kLaneBytes = 2u << 20;  // small enough that the DMA engine starts early in every call, large enough for full PCIe rate
 
 struct Staging {
     int lanes = 0;
+    int device = 0;
     uint8_t* block = nullptr;  // lanes * 2 * kLaneBytes of pinned memory
     cudaStream_t copy[kMaxLanes] = {};
     cudaEvent_t done[kMaxLanes][2] = {};
     uint8_t* buf(int lane, int b) const { return block + ((size_t)lane * 2 + b) * kLaneBytes; }
+
+    // Lane threads 1 .. lanes-1 live as long as the context (lane 0 is the calling thread): a call publishes a job, the
+    // threads run job(lane) and report back.  Starting threads per call cost about 2 ms per 128 MB piece.
+    std::vector<std::thread> pool;
+    std::mutex mu;
+    std::condition_variable wake, finished;
+    std::function<int(int)> job;
+    uint64_t generation = 0;
+    int active = 0, pending = 0, first_error = 0;
+    bool quit = false;
+
+    void lane_main(int lane) {
+        cudaSetDevice(device);
+        uint64_t seen = 0;
+        for (;;) {
+            std::function<int(int)> mine;
+            {
+                std::unique_lock<std::mutex> lock(mu);
+                wake.wait(lock, [&] { return quit || generation != seen; });
+                if (quit) return;
+                seen = generation;
+                if (lane >= active) continue;
+                mine = job;
+            }
+            const int rc = mine(lane);
+            {
+                std::lock_guard<std::mutex> lock(mu);
+                if (rc && !first_error) first_error = rc;
+                if (--pending == 0) finished.notify_all();
+            }
+        }
+    }
+
+    // Runs work(lane) on min(lanes, n_chunks) lanes; returns the first non-zero result.
+    int run(uint64_t n_chunks, std::function<int(int)> work) {
+        const int T = (int)std::min<uint64_t>((uint64_t)lanes, std::max<uint64_t>(1, n_chunks));
+        if (T > 1) {
+            std::lock_guard<std::mutex> lock(mu);
+            job = work;
+            active = T;
+            pending = T - 1;
+            first_error = 0;
+            generation++;
+        }
+        if (T > 1) wake.notify_all();
+        const int rc0 = work(0);
+        if (T == 1) return rc0;
+        std::unique_lock<std::mutex> lock(mu);
+        finished.wait(lock, [&] { return pending == 0; });
+        return rc0 ? rc0 : first_error;
+    }
 };
 
 int n_io_lanes() {
@@ -44,21 +99,38 @@ int n_io_lanes() {
     return (int)std::max(2u, std::min((unsigned)kMaxLanes, hw / share));
 }
 
-Staging* staging_of(bpe_ctx* ctx) {
-    if (ctx->io_staging) return static_cast<Staging*>(ctx->io_staging);
+void staging_free(Staging* st) {
+    {
+        std::lock_guard<std::mutex> lock(st->mu);
+        st->quit = true;
+    }
+    st->wake.notify_all();
+    for (auto& t : st->pool) t.join();
+    for (int l = 0; l < kMaxLanes; l++) {
+        if (st->copy[l]) cudaStreamDestroy(st->copy[l]);
+        for (int b = 0; b < 2; b++) if (st->done[l][b]) cudaEventDestroy(st->done[l][b]);
+    }
+    if (st->block) cudaFreeHost(st->block);
+    delete st;
+}
+
+Staging* staging_of(bpe_ctx* ctx, int which) {
+    if (ctx->io_staging[which]) return static_cast<Staging*>(ctx->io_staging[which]);
     Staging* st = new Staging();
     st->lanes = n_io_lanes();
+    st->device = ctx->device;
     bool ok = cudaHostAlloc((void**)&st->block, (size_t)st->lanes * 2 * kLaneBytes, cudaHostAllocDefault) == cudaSuccess;
     for (int l = 0; ok && l < st->lanes; l++)
         ok = cudaStreamCreateWithFlags(&st->copy[l], cudaStreamNonBlocking) == cudaSuccess &&
              cudaEventCreateWithFlags(&st->done[l][0], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&st->done[l][1], cudaEventDisableTiming) == cudaSuccess;
-    ctx->io_staging = st;
     if (!ok) {
         ctx_fail(ctx, BPE_ERR_CUDA, "allocating pinned staging buffers", cudaGetLastError());
-        io_staging_free(ctx);
+        staging_free(st);
         return nullptr;
     }
+    for (int l = 1; l < st->lanes; l++) st->pool.emplace_back([st, l] { st->lane_main(l); });
+    ctx->io_staging[which] = st;
     return st;
 }
 
@@ -72,31 +144,13 @@ bool pread_all(int fd, uint8_t* dst, size_t n, uint64_t off) {
     return true;
 }
 
-// Runs work(lane) on st->lanes threads (fewer for small jobs); returns the first non-zero result.
-template <class F>
-int run_lanes(const Staging* st, uint64_t n_chunks, F work) {
-    const int T = (int)std::min<uint64_t>((uint64_t)st->lanes, std::max<uint64_t>(1, n_chunks));
-    std::vector<int> rc(T, 0);
-    std::vector<std::thread> th;
-    for (int l = 1; l < T; l++) th.emplace_back([&rc, &work, l] { rc[l] = work(l); });
-    rc[0] = work(0);
-    for (auto& x : th) x.join();
-    for (int v : rc) if (v) return v;
-    return 0;
-}
-
 }  // namespace
 
 void io_staging_free(bpe_ctx* ctx) {
-    if (!ctx->io_staging) return;
-    Staging* st = static_cast<Staging*>(ctx->io_staging);
-    for (int l = 0; l < kMaxLanes; l++) {
-        if (st->copy[l]) cudaStreamDestroy(st->copy[l]);
-        for (int b = 0; b < 2; b++) if (st->done[l][b]) cudaEventDestroy(st->done[l][b]);
+    for (int which = 0; which < 2; which++) {
+        if (ctx->io_staging[which]) staging_free(static_cast<Staging*>(ctx->io_staging[which]));
+        ctx->io_staging[which] = nullptr;
     }
-    if (st->block) cudaFreeHost(st->block);
-    delete st;
-    ctx->io_staging = nullptr;
 }
 
 // Lane results: 1 = short read, 2 = CUDA error.
@@ -104,15 +158,13 @@ extern "C" int bpe_load_file(bpe_ctx* ctx, const char* path, uint64_t offset, ui
     if (!ctx || !path || (n && !d_dst)) return ctx ? ctx_fail(ctx, BPE_ERR_ARGUMENT, "bpe_load_file arguments") : BPE_ERR_ARGUMENT;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     if (n == 0) return BPE_OK;
-    Staging* st = staging_of(ctx);
+    Staging* st = staging_of(ctx, 0);
     if (!st) return BPE_ERR_CUDA;
     int fd = open(path, O_RDONLY);
     if (fd < 0) return ctx_fail(ctx, BPE_ERR_ARGUMENT, "cannot open file");
     const uint64_t n_chunks = (n + kLaneBytes - 1) / kLaneBytes;
     std::atomic<uint64_t> next{0};
-    const int device = ctx->device;
-    int rc = run_lanes(st, n_chunks, [&](int lane) -> int {
-        if (cudaSetDevice(device) != cudaSuccess) return 2;
+    int rc = st->run(n_chunks, [&](int lane) -> int {
         int bad = 0;
         for (int it = 0;; it++) {
             const uint64_t c = next.fetch_add(1);
@@ -138,16 +190,14 @@ extern "C" int bpe_store_to_host(bpe_ctx* ctx, const void* d_src, uint64_t n, vo
     if (!ctx || (n && (!d_src || !h_dst))) return ctx ? ctx_fail(ctx, BPE_ERR_ARGUMENT, "bpe_store_to_host arguments") : BPE_ERR_ARGUMENT;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     if (n == 0) return BPE_OK;
-    Staging* st = staging_of(ctx);
+    Staging* st = staging_of(ctx, 1);
     if (!st) return BPE_ERR_CUDA;
     CUDA_TRY(ctx, cudaStreamSynchronize((cudaStream_t)stream));  // the producer of d_src has finished
     const uint8_t* src = static_cast<const uint8_t*>(d_src);
     uint8_t* dst = static_cast<uint8_t*>(h_dst);
     const uint64_t n_chunks = (n + kLaneBytes - 1) / kLaneBytes;
     std::atomic<uint64_t> next{0};
-    const int device = ctx->device;
-    int rc = run_lanes(st, n_chunks, [&](int lane) -> int {
-        if (cudaSetDevice(device) != cudaSuccess) return 2;
+    int rc = st->run(n_chunks, [&](int lane) -> int {
         // the chunk copied in round it is moved to the destination in round it + 1, while the next chunk is in flight
         uint64_t prev_chunk = ~0ull;
         size_t prev_len = 0;

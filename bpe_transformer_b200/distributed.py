@@ -147,7 +147,7 @@ def encode_file_sharded(tokenizer, path, group=None) -> tuple[np.ndarray, int, i
     engine = _lib.get_engine()
     offs = line_shard_offsets(path, world)
     lo, hi = offs[rank], offs[rank + 1]
-    ids = tokenizer.encode_device_to_array(engine.load_file(path, lo, hi), engine)
+    ids = tokenizer.encode_file_to_array(path, engine=engine, lo=lo, hi=hi)
     counts = [torch.zeros(1, dtype=torch.int64, device=f"cuda:{engine.device}") for _ in range(world)]
     dist.all_gather(counts, torch.tensor([len(ids)], dtype=torch.int64, device=f"cuda:{engine.device}"), group=group)
     counts = [int(c.item()) for c in counts]

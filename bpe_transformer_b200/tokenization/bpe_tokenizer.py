@@ -3,6 +3,7 @@ runs in csrc/scan.cu, count.cu and encode.cu through the C-ABI (include/bpe_b200
 from __future__ import annotations
 
 import io
+import os
 import pickle
 from collections.abc import Iterable, Iterator
 from pathlib import Path
@@ -15,6 +16,36 @@ from .tokenizer import Tokenizer
 
 _MISSING = 0xFFFFFFFF
 _BATCH_BYTES = 64 << 20  # encode_iterable hands the GPU about this much text at a time
+
+
+_PIPE_BYTES = int(os.environ.get("BPE_B200_PIPE_BYTES", str(128 << 20)))  # piece size of the load / encode / store pipeline
+
+
+def _cuts_after_newlines(path, lo: int, hi: int, piece: int) -> list[int]:
+    """Offsets lo = o0 < o1 < ... = hi with every inner offset just behind the first newline at or after lo + k * piece."""
+    offs = [lo]
+    with open(path, "rb") as fh:
+        target = lo + piece
+        while target < hi:
+            pos = max(target, offs[-1])
+            fh.seek(pos)
+            found = hi
+            while pos < hi:
+                window = fh.read(min(1 << 16, hi - pos))
+                if not window:
+                    break
+                i = window.find(b"\n")
+                if i != -1:
+                    found = pos + i + 1
+                    break
+                pos += len(window)
+            if found >= hi:
+                break
+            if found > offs[-1]:
+                offs.append(found)
+            target = max(target + piece, found)
+    offs.append(hi)
+    return offs
 
 
 class BPETokenizer(Tokenizer):
@@ -206,12 +237,95 @@ class BPETokenizer(Tokenizer):
         if tail:
             yield from self._ids_to_numpy(self.encode_bytes_to_device(tail.encode(ENCODING_STD), flags=_lib.CUT_AFTER_NEWLINE)).tolist()
 
-    def encode_file_to_array(self, path, cut_after_newline: bool = True, engine: "_lib.Engine | None" = None) -> np.ndarray:
-        """Array-returning sibling of encode_iterable(open(path)): the whole UTF-8 file -> numpy uint16 / uint32
-        ids (the format a 1-D token dataset uses).  Files with '\\r' go through Python's universal-newline
-        translation first, as open(path) would do."""
+    def encode_file_to_array(self, path, cut_after_newline: bool = True, engine: "_lib.Engine | None" = None,
+                             lo: int = 0, hi: int | None = None) -> np.ndarray:
+        """Array-returning sibling of encode_iterable(open(path)): the UTF-8 file (or its bytes [lo, hi), which must
+        start and end at line ends) -> numpy uint16 / uint32 ids (the format a 1-D token dataset uses).  Files
+        with '\\r' go through Python's universal-newline translation first, as open(path) would do.
+        Large files move in pieces cut after a newline: one host thread reads the next piece into HBM and another
+        copies the previous piece's ids out while the GPU encodes the current one."""
         engine = engine or _lib.get_engine()
-        return self.encode_device_to_array(engine.load_file(path), engine, cut_after_newline)
+        size = os.path.getsize(path)
+        hi = size if hi is None else min(hi, size)
+        if cut_after_newline and hi - lo > _PIPE_BYTES + _PIPE_BYTES // 2:
+            ids = self._encode_file_pipelined(path, lo, hi, engine)
+            if ids is not None:
+                return ids
+        return self.encode_device_to_array(engine.load_file(path, lo, hi), engine, cut_after_newline)
+
+    def _encode_file_pipelined(self, path, lo: int, hi: int, engine: "_lib.Engine"):
+        """None if the file holds a '\\r' (the caller then takes the whole-file path with newline translation)."""
+        import queue
+        import threading
+
+        import torch
+
+        offs = _cuts_after_newlines(path, lo, hi, _PIPE_BYTES)
+        wide = self._bind(engine)
+        out = _lib.host_array(hi - lo, np.uint32 if wide else np.uint16)  # one id per byte at most; unused pages stay untouched
+        loaded: queue.Queue = queue.Queue(maxsize=2)
+        to_store: queue.Queue = queue.Queue(maxsize=2)
+        errors: list[BaseException] = []
+        stop = threading.Event()
+
+        def loader():
+            try:
+                torch.cuda.set_device(engine.device)
+                for a, b in zip(offs[:-1], offs[1:]):
+                    if stop.is_set():
+                        break
+                    loaded.put(engine.load_file(path, a, b))
+            except BaseException as e:  # noqa: BLE001 - re-raised on the calling thread
+                errors.append(e)
+            finally:
+                loaded.put(None)
+
+        def storer():
+            failed = False
+            torch.cuda.set_device(engine.device)
+            while True:
+                item = to_store.get()
+                if item is None:
+                    return
+                if failed:
+                    continue
+                try:
+                    ids, at = item
+                    engine.store_into(ids, out[at:at + int(ids.numel())])
+                except BaseException as e:  # noqa: BLE001
+                    errors.append(e)
+                    failed = True
+                    stop.set()
+
+        threads = [threading.Thread(target=loader, daemon=True), threading.Thread(target=storer, daemon=True)]
+        for t in threads:
+            t.start()
+        total, has_cr = 0, False
+        while True:
+            item = loaded.get()
+            if item is None:
+                break
+            if stop.is_set():
+                continue  # drain what the loader had in flight
+            d_text, n = item
+            try:
+                if n and bool((d_text[:n] == 13).any().item()):
+                    has_cr = True
+                    stop.set()
+                    continue
+                ids = self.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=engine, on_device=(d_text, n))
+            except BaseException as e:  # noqa: BLE001
+                errors.append(e)
+                stop.set()
+                continue
+            to_store.put((ids, total))
+            total += int(ids.numel())
+        to_store.put(None)
+        for t in threads:
+            t.join()
+        if errors:
+            raise errors[0]
+        return None if has_cr else out[:total]
 
     def encode_device_to_array(self, on_device, engine: "_lib.Engine", cut_after_newline: bool = True) -> np.ndarray:
         """(padded device text, length) -> NumPy ids, cutting after every newline like a file handle's line iteration."""

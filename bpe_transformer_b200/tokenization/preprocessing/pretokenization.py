@@ -23,6 +23,9 @@ from ... import _lib
 from ...settings import ENCODING_STD
 
 
+_PIPE_BYTES = int(os.environ.get("BPE_B200_PIPE_BYTES", str(128 << 20)))  # piece size of the load / count pipeline
+
+
 # --------------------------------------------------------------------------------------------------------
 # host helpers that mirror reference functions
 # --------------------------------------------------------------------------------------------------------
@@ -127,6 +130,16 @@ def count_into_engine(engine: "_lib.Engine", file_path, special_tokens: list[str
         # starts, where a segment ends anyway.)
         with open(file_path, "rb") as fh:
             cuts = find_chunk_boundaries(fh, n_chunks, None)[1:-1]
+    if specials and os.path.getsize(file_path) > _PIPE_BYTES + _PIPE_BYTES // 2:
+        while True:
+            done = _count_file_pipelined(engine, file_path, special_tokens)
+            if done == "counted":
+                return
+            engine.unique_reset()
+            if done == "invalid-utf8":
+                break  # whole-file path below, which repairs the bytes on the host
+            if not engine.grow():  # "capacity"
+                raise _lib.BpeError(_lib.ERR_CAPACITY, "table of distinct pretokens cannot grow further")
     d_text, n = engine.load_file(file_path)
     try:
         mask = engine.scan(d_text, n, cuts=cuts)
@@ -136,6 +149,63 @@ def count_into_engine(engine: "_lib.Engine", file_path, special_tokens: list[str
         d_text, n = engine.to_device(clean)
         mask = engine.scan(d_text, n, cuts=cuts)
     count_with_growth(engine, d_text, n, mask)
+
+
+def _count_file_pipelined(engine: "_lib.Engine", file_path, special_tokens: list[str]) -> str:
+    """Large corpora with special tokens: pieces cut at special-token starts (the reference's own chunk rule, so the
+    cuts cannot change the result) are read into HBM by a host thread while the GPU scans and counts the piece
+    before.  Returns "counted", or why the caller has to start again: "capacity" / "invalid-utf8"."""
+    import queue
+    import threading
+
+    import torch
+
+    size = os.path.getsize(file_path)
+    with open(file_path, "rb") as fh:
+        offs = find_chunk_boundaries(fh, max(2, -(-size // _PIPE_BYTES)), special_tokens)
+    loaded: queue.Queue = queue.Queue(maxsize=2)
+    errors: list[BaseException] = []
+    stop = threading.Event()
+
+    def loader():
+        try:
+            torch.cuda.set_device(engine.device)
+            for a, b in zip(offs[:-1], offs[1:]):
+                if stop.is_set():
+                    break
+                loaded.put(engine.load_file(file_path, a, b))
+        except BaseException as e:  # noqa: BLE001 - re-raised on the calling thread
+            errors.append(e)
+        finally:
+            loaded.put(None)
+
+    thread = threading.Thread(target=loader, daemon=True)
+    thread.start()
+    outcome = "counted"
+    while True:
+        item = loaded.get()
+        if item is None:
+            break
+        if stop.is_set():
+            continue
+        d_text, n = item
+        try:
+            engine.count(d_text, n, engine.scan(d_text, n))
+        except _lib.InvalidUtf8:
+            outcome = "invalid-utf8"
+            stop.set()
+        except _lib.BpeError as e:
+            if e.code != _lib.ERR_CAPACITY:
+                errors.append(e)
+            outcome = "capacity"
+            stop.set()
+        except BaseException as e:  # noqa: BLE001
+            errors.append(e)
+            stop.set()
+    thread.join()
+    if errors:
+        raise errors[0]
+    return outcome
 
 
 def count_with_growth(engine: "_lib.Engine", d_text, n: int, mask, keep_counted: bool = False) -> None:

@@ -64,12 +64,16 @@ int bpe_set_special_tokens(bpe_ctx* ctx, const uint8_t* h_blob, const uint32_t* 
 
 /* ---- host I/O staging (the step before and after the path) ----------------------------------- */
 
-/* Reads bytes [offset, offset + n) of the file at `path` into the device buffer d_dst: several reader threads fill
- * persistent pinned staging buffers while the previous chunk is copied to the GPU.  Replaces the f.seek / f.read of
- * the reference's workers (pretokenization.py:192-194).  The copy has completed on return. */
+/* Reads bytes [offset, offset + n) of the file at `path` into the device buffer d_dst: up to 16 host threads, each
+ * with its own copy stream and pair of persistent pinned buffers, read 2 MB pieces and copy them to the GPU.
+ * Replaces the f.seek / f.read of the reference's workers (pretokenization.py:192-194).  The copy has completed on
+ * return.  The two I/O calls are the exception to "one call at a time per context": ONE bpe_load_file and ONE
+ * bpe_store_to_host may run (from other host threads) while another call works on the same context, which is how the
+ * Python layer overlaps reading the next piece of a file with encoding this one and storing the previous one.
+ * Thread count: BPE_B200_IO_THREADS, default min(16, cores / LOCAL_WORLD_SIZE). */
 int bpe_load_file(bpe_ctx* ctx, const char* path, uint64_t offset, uint64_t n, uint8_t* d_dst, void* stream);
 
-/* Copies n bytes from device memory to an ordinary (pageable) host array through the same staging buffers, e.g. the
+/* Copies n bytes from device memory to an ordinary (pageable) host array through staging buffers of its own, e.g. the
  * ids of bpe_encode into a NumPy array — the 1-D token dataset format.  Waits for `stream` first. */
 int bpe_store_to_host(bpe_ctx* ctx, const void* d_src, uint64_t n, void* h_dst, void* stream);
 

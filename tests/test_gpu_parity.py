@@ -6,6 +6,7 @@ bit-exact: identical start masks, Counters, ordered merges, vocab dicts and toke
 """
 from __future__ import annotations
 
+import os
 import random
 from collections import Counter
 
@@ -368,6 +369,44 @@ def test_encode_keyerror_is_raised_every_time(gpt2_model):
         with pytest.raises(KeyError):
             tok.encode("a plain zebra sentence")
         assert tok.encode("a plain sentence") == fine
+
+
+def test_pipelined_file_paths_match_whole_file_paths(tmp_path, ts10k_model, monkeypatch):
+    """Large files are read, processed and stored piece by piece on three host threads; with a small piece size the
+    same code must give what the whole-file path gives: pretoken counts, trained model, ids, '\\r' handling."""
+    from adapters import get_tokenizer, run_train_bpe
+    from bpe_transformer_b200.tokenization import bpe_tokenizer as tk
+    from bpe_transformer_b200.tokenization.preprocessing import pretokenization as pt
+
+    path = synth_corpus(0, 71, 6_000_000, str(tmp_path / "c.txt"))
+    whole_model = run_train_bpe(path, 1500, [EOT])
+    whole_counts = pt.parallel_pretokenization(path, special_tokens=[EOT])
+    vocab, merges = ts10k_model
+    tok = get_tokenizer(with_specials(vocab, [EOT]), merges, [EOT])
+    whole_ids = tok.encode_file_to_array(path)
+    monkeypatch.setattr(pt, "_PIPE_BYTES", 1 << 20)
+    monkeypatch.setattr(tk, "_PIPE_BYTES", 1 << 20)
+    assert pt.parallel_pretokenization(path, special_tokens=[EOT]) == whole_counts
+    assert run_train_bpe(path, 1500, [EOT]) == whole_model
+    ids = tok.encode_file_to_array(path)
+    assert ids.dtype == whole_ids.dtype and np.array_equal(ids, whole_ids)
+    size = os.path.getsize(path)
+    cuts = tk._cuts_after_newlines(path, 0, size, size // 3)
+    parts = [tok.encode_file_to_array(path, lo=a, hi=b) for a, b in zip(cuts[:-1], cuts[1:])]
+    assert np.array_equal(np.concatenate(parts), whole_ids)
+    # a carriage return anywhere sends the file through the newline-translating path
+    data = open(path, "rb").read()
+    cr = tmp_path / "cr.txt"
+    cr.write_bytes(data[:3_000_000] + b"one\r\ntwo\rthree\n" + data[3_000_000:])
+    with open(cr, encoding="utf-8") as fh:
+        want = list(tok.encode_iterable(fh))
+    assert tok.encode_file_to_array(str(cr)).tolist() == want
+    # invalid UTF-8 in a late piece: counted like the reference's errors="ignore" decoding
+    bad = tmp_path / "bad.txt"
+    bad.write_bytes(data[:4_000_000] + b" caf\xc3 \xff\xfe ok " + data[4_000_000:])
+    got = pt.parallel_pretokenization(str(bad), special_tokens=[EOT])
+    monkeypatch.setattr(pt, "_PIPE_BYTES", 1 << 40)
+    assert got == pt.parallel_pretokenization(str(bad), special_tokens=[EOT])
 
 
 def test_model_and_dataset_formats(tmp_path, gpt2_model, input_bytes, tmp_file):
