@@ -367,12 +367,27 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
         kernels["encode:" + name] = {"ms": ms, "launches": n}
     hbm_kernels = {k: gbps(n_local, k_train[k][0]) for k in ("scan_kernel", "count_kernel") if k in k_train and k_train[k][0]}
     dominant = min(hbm_kernels, key=hbm_kernels.get) if hbm_kernels else None
+    # DRAM bytes per launch from the committed `ncu --set full` capture (tools/ncu_summary.py); only quoted for the
+    # corpus size it was taken on, one GPU.
+    traffic_file = ROOT / "profiles" / "r01_ncu_dram_bytes_per_launch_2.1GB.json"
+    ncu_traffic = {}
+    if traffic_file.exists() and world == 1 and abs(total - 2_100_000_403) < 1_000_000:
+        ncu_traffic = json.loads(traffic_file.read_text())
+    ncu_name = {"scan_kernel": "scan_kernel<0>", "count_kernel": "count_kernel", "emit_fused_kernel": "emit_fused_kernel<unsigned short>"}
     roofline = None
     if dominant:
+        others = {k: {"achieved": v, "frac": v / peak, "traffic": ncu_traffic.get(ncu_name[k])} for k, v in hbm_kernels.items() if k != dominant}
+        if k_enc.get("emit_fused_kernel", (0, 0))[0]:
+            emit_bytes = int(n_enc + ids.numel() * ids.element_size())  # N read + 2 T written
+            v = gbps(emit_bytes, k_enc["emit_fused_kernel"][0])
+            others["encode:emit_fused_kernel"] = {"achieved": v, "frac": v / peak, "traffic": ncu_traffic.get(ncu_name["emit_fused_kernel"]),
+                                                  "algorithmic_bytes_per_launch": emit_bytes}
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": hbm_kernels[dominant], "peak": peak, "unit": "GB/s",
-                    "frac": hbm_kernels[dominant] / peak, "traffic": None, "peak_source": peak_src,
+                    "frac": hbm_kernels[dominant] / peak, "traffic": ncu_traffic.get(ncu_name[dominant]), "peak_source": peak_src,
+                    "traffic_source": "profiles/r01_ncu_dram_bytes_per_launch_2.1GB.json (ncu --set full, dram read + write, per launch)" if ncu_traffic else None,
                     "algorithmic_bytes_per_launch": n_local,
-                    "others": {k: {"achieved": v, "frac": v / peak} for k, v in hbm_kernels.items() if k != dominant}}
+                    "note": "scan/count/emit are instruction-issue bound, not HBM bound (DESIGN.md section 4); the merge loop is latency bound and reported as us_per_merge",
+                    "others": others}
 
     line = {
         "metric": METRIC, "value": step_ms / 1e3, "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

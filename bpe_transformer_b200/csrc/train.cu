@@ -75,6 +75,7 @@ struct Ctrl {
     Command cmd;
     unsigned int dbg[8];      // flags bit 1: [0] stale cache copies, [1] first iteration with one, [2] hot pairs missing from the cache, [3] first iteration
     unsigned long long phase_clk[8];  // developer trace: SM cycles of the driver's thread 0 per phase, summed over iterations
+    unsigned long long sub_clk[8];    // developer trace: inside the argmax (scan, barrier, ties, barrier, order + barrier)
 };
 
 struct TrainState {
@@ -112,6 +113,22 @@ __device__ __forceinline__ uint64_t pair_slot(const TrainState& S, unsigned long
     return 0;
 }
 
+// The same search when the first compare-and-swap has been issued earlier (its latency hidden behind other loads).
+__device__ __forceinline__ uint64_t pair_slot_resume(const TrainState& S, unsigned long long key, uint64_t slot, unsigned long long cur) {
+    for (int probe = 0; probe < PAIR_PROBE_LIMIT; probe++) {
+        if (cur == 0) {
+            unsigned int idx = atomicAdd(&S.ctrl->n_live, 1u);
+            S.live[idx] = (uint32_t)slot;
+            return slot;
+        }
+        if (cur == key) return slot;
+        slot = (slot + 1) & S.ph_mask;
+        cur = atomicCAS(S.ph_key + slot, 0ull, key);
+    }
+    set_status(S.status, ST_PAIR_TABLE_FULL);
+    return 0;
+}
+
 // Count updates straight to the global table.  A pair whose count rises to or above the threshold is appended to the
 // global "pending hot" list, which the driver drains (duplicates are harmless there).
 struct GlobalAdder {
@@ -137,14 +154,16 @@ struct GlobalAdder {
 // the keys.  The global table stays exact (every update goes there too, fire-and-forget); the copy lets the argmax of a
 // light step run without touching global memory.  Entries appended during a step get their count from global memory
 // when the step closes; after a heavy step (other CTAs updated counts) all copies are reloaded.
-#define HC 6144u      // cache entries
-#define CACHE_FILL 3072u  // entries a rebuild aims for (the rest is room for pairs that rise past T)
+#define HC 4096u      // cache entries
+#define CACHE_FILL 2048u  // entries a rebuild aims for (the rest is room for pairs that rise past T)
+#define PRE_UNKNOWN (~0ull)  // HotCache::pre of an entry whose prefix key has not been fetched (yet): ties go to global memory
 #define SUB_BINS 1024u
-#define HIDX 16384u   // index slots (power of two)
+#define HIDX 8192u    // index slots (power of two)
 struct HotCache {
     unsigned long long key[HC];  // 0 = hole (duplicate that lost the race)
     long long cnt[HC];
     uint32_t slot[HC];
+    unsigned long long pre[HC];  // tk_pre of the pair's FIRST token: most ties in count are decided without leaving shared memory
     unsigned short index[HIDX];  // entry + 1, 0 = empty
     unsigned int n;              // entries in use (may exceed HC: overflow, forces a rebuild)
 };
@@ -163,21 +182,22 @@ __device__ __forceinline__ int hc_find(const HotCache& H, unsigned long long key
 }
 
 // Appends (key, slot) with count `cnt`; a concurrent duplicate loses and becomes a hole.
-__device__ __forceinline__ void hc_append(HotCache& H, unsigned long long key, uint32_t slot, long long cnt) {
+__device__ __forceinline__ int hc_append(HotCache& H, unsigned long long key, uint32_t slot, long long cnt, unsigned long long pre = PRE_UNKNOWN) {
     unsigned int idx = atomicAdd(&H.n, 1u);
-    if (idx >= HC) return;
-    H.key[idx] = key; H.slot[idx] = slot; H.cnt[idx] = cnt;
+    if (idx >= HC) return -1;
+    H.key[idx] = key; H.slot[idx] = slot; H.cnt[idx] = cnt; H.pre[idx] = pre;
     __threadfence_block();
     uint32_t h = hc_hash(key) & (HIDX - 1);
     for (uint32_t probe = 0; probe < HIDX; probe++) {
         unsigned short v = *reinterpret_cast<volatile unsigned short*>(&H.index[h]);
         if (v == 0) {
             v = atomicCAS(&H.index[h], (unsigned short)0, (unsigned short)(idx + 1));
-            if (v == 0) return;
+            if (v == 0) return (int)idx;
         }
-        if (H.key[v - 1] == key) { H.key[idx] = 0; return; }
+        if (H.key[v - 1] == key) { H.key[idx] = 0; H.cnt[idx] = RETIRED; return -1; }
         h = (h + 1) & (HIDX - 1);
     }
+    return -1;
 }
 
 struct CacheAdder {
@@ -200,6 +220,107 @@ struct CacheAdder {
         long long before = (long long)atomicAdd(reinterpret_cast<unsigned long long*>(S.ph_cnt + slot), (unsigned long long)delta);
         if (before < threshold && before + delta >= threshold) hc_append(H, key, (uint32_t)slot, 0);  // count: loaded when the step closes
     }
+};
+
+// ---- light steps without waiting for global memory ------------------------------------------------------------------------
+// Two facts about the reference's deltas (rewrite_word_warp below): every count that a step ADDS belongs to a pair that
+// contains the step's new token x, i.e. to a pair that did not exist before the step; every pair that existed before
+// only ever loses count.  So, in a light step,
+//   * additions are summed in a small shared-memory table keyed by (other token, side).  When the step closes the table
+//     holds the exact count of every new pair: those >= T enter the cache with that count (nothing to read back), and
+//     all of them are handed to the deferred queue as one (key, +count) item each;
+//   * subtractions from cached pairs update the cached copy at once and post a fire-and-forget update to the global
+//     table; subtractions from uncached pairs (which can never become hot again) go to the deferred queue;
+//   * the deferred queue is applied to the global table (slot lookup + add) at the start of the NEXT step, by threads
+//     that are waiting for that step's posting lists anyway, and always before anything reads global counts (cache
+//     rebuild, heavy step).  A new cached pair learns its global slot there, before any later step can subtract from it.
+#define NPS 1024u     // new-pair slots per step (power of two); a fuller step falls back to CacheAdder for the rest
+#define DQ_CAP 1024u  // deferred updates; a fuller queue applies the update on the spot
+struct NewPairs {
+    uint32_t key[NPS];  // ((other << 1) | side) + 1, side 1 = (x, other), 0 = (other, x); 0 = empty
+    long long cnt[NPS];
+    unsigned int overflow;  // some addition of this step went through CacheAdder
+};
+struct Deferred {
+    unsigned long long key[DQ_CAP];
+    long long delta[DQ_CAP];
+    unsigned short entry[DQ_CAP];  // cache entry that waits for its global slot, 0xFFFF = none
+    unsigned int n;
+};
+
+__device__ __forceinline__ void global_add(const TrainState& S, uint64_t slot, long long delta) {
+    atomicAdd(reinterpret_cast<unsigned long long*>(S.ph_cnt + slot), (unsigned long long)delta);
+}
+
+// One deferred item: find (or claim) the pair's slot, post the update, tell the cache entry its slot.
+__device__ __forceinline__ void deferred_apply(const TrainState& S, HotCache& H, unsigned long long key, long long delta, unsigned short entry) {
+    const uint64_t slot = pair_slot(S, key);
+    global_add(S, slot, delta);
+    if (entry != 0xFFFFu) {
+        H.slot[entry] = (uint32_t)slot;
+        if (H.pre[entry] == PRE_UNKNOWN) H.pre[entry] = __ldcg(S.tk_pre + (uint32_t)((key - 1) >> 32));
+    }
+}
+
+__device__ __forceinline__ void deferred_push(const TrainState& S, HotCache& H, Deferred& DQ, unsigned long long key, long long delta, unsigned short entry) {
+    const unsigned int q = atomicAdd(&DQ.n, 1u);
+    if (q < DQ_CAP) { DQ.key[q] = key; DQ.delta[q] = delta; DQ.entry[q] = entry; }
+    else deferred_apply(S, H, key, delta, entry);
+}
+
+// Applies everything that is queued (all threads of the CTA call this; ends with a barrier, queue empty, updates landed).
+template <int NT>
+__device__ __forceinline__ void deferred_drain(const TrainState& S, HotCache& H, Deferred& DQ) {
+    __syncthreads();
+    const unsigned int n = min(DQ.n, DQ_CAP);
+    for (unsigned int i = threadIdx.x; i < n; i += NT) deferred_apply(S, H, DQ.key[i], DQ.delta[i], DQ.entry[i]);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) DQ.n = 0;
+    __syncthreads();
+}
+
+struct LightAdder {
+    const TrainState& S;
+    HotCache& H;
+    NewPairs& NP;
+    Deferred& DQ;
+    long long threshold;
+    uint32_t x;
+    __device__ __forceinline__ void operator()(uint32_t a, uint32_t b, long long delta) const {
+        if (delta > 0) {  // (a, x) or (x, b) or (x, x): a pair born in this step
+            const uint32_t code = (a == x ? ((b << 1) | 1u) : (a << 1)) + 1u;
+            uint32_t h = (code * 0x9E3779B1u) >> 22;  // 10 bits
+            for (uint32_t probe = 0; probe < NPS; probe++) {
+                uint32_t cur = *reinterpret_cast<volatile uint32_t*>(&NP.key[h]);
+                if (cur == 0) cur = atomicCAS(&NP.key[h], 0u, code);
+                if (cur == 0 || cur == code) {
+                    atomicAdd(reinterpret_cast<unsigned long long*>(&NP.cnt[h]), (unsigned long long)delta);
+                    return;
+                }
+                h = (h + 1) & (NPS - 1);
+            }
+            NP.overflow = 1;
+            CacheAdder{S, H, threshold}(a, b, delta);
+            return;
+        }
+        const unsigned long long key = (((unsigned long long)a << 32) | b) + 1ull;
+        const int e = hc_find(H, key);
+        if (e >= 0) {
+            atomicAdd(reinterpret_cast<unsigned long long*>(&H.cnt[e]), (unsigned long long)delta);
+            global_add(S, H.slot[e], delta);
+            return;
+        }
+        deferred_push(S, H, DQ, key, delta, 0xFFFFu);
+    }
+};
+
+struct DriverShared {  // the driver CTA's dynamic shared memory
+    HotCache H;
+    NewPairs NP;
+    Deferred DQ;
+    uint32_t tie[MAX_TIES];      // cache entries (or global slots) that share the top count
+    unsigned int sub[SUB_BINS];  // rebuild: histogram inside the threshold's power-of-two bin
 };
 
 // ---- build the word table from the table of distinct pretokens (bpe_trainer.py:188-190: len 1 is skipped) ----
@@ -266,12 +387,9 @@ __device__ __forceinline__ Best shfl_best(const Best& b, int o, bool down) {
 
 // ---- word rewriting -----------------------------------------------------------------------------------------------------
 // Does the word contain (a, b)?  One thread, 16-byte loads (independent of one another, so they overlap).
-__device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, uint32_t off, uint32_t a, uint32_t b, uint32_t* len_out) {
-    const uint4* s4 = reinterpret_cast<const uint4*>(S.sym + off);
-    uint4 v = __ldcg(s4);                        // every word owns at least 4 symbol slots: load before the length is known
-    const uint32_t len = __ldcg(S.w_len + w);
-    *len_out = len;
+__device__ __forceinline__ bool word_has_pair_loaded(const TrainState& S, uint32_t off, uint4 v, uint32_t len, uint32_t a, uint32_t b) {
     if (len < 2) return false;
+    const uint4* s4 = reinterpret_cast<const uint4*>(S.sym + off);
     bool hit = (v.x == a && v.y == b) | (2 < len && v.y == a && v.z == b) | (3 < len && v.z == a && v.w == b);
     uint32_t prev = v.w;
     for (uint32_t k = 4; k < len; k += 4) {
@@ -281,6 +399,13 @@ __device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, u
         prev = v.w;
     }
     return hit;
+}
+
+__device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, uint32_t off, uint32_t a, uint32_t b, uint32_t* len_out) {
+    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(S.sym + off));  // every word owns at least 4 symbol slots: load before the length is known
+    const uint32_t len = __ldcg(S.w_len + w);
+    *len_out = len;
+    return word_has_pair_loaded(S, off, v, len, a, b);
 }
 
 // One word, one thread: replace (a, b) by x left to right without overlap, apply the reference's count deltas.
@@ -324,6 +449,7 @@ __device__ bool rewrite_word_serial(const TrainState& S, uint32_t w, uint32_t of
 template <class Adder>
 __device__ bool rewrite_word_warp(const TrainState& S, uint32_t w, uint32_t off, uint32_t len, uint32_t a, uint32_t b, uint32_t x, const Adder& add) {
     const uint32_t lane = threadIdx.x & 31;
+    if (len == 0xFFFFu) len = __ldcg(S.w_len + w);  // the queue keeps 16 bits
     if (len < 2) return false;
     if (len > 32) {
         bool hit = lane == 0 ? rewrite_word_serial(S, w, off, len, a, b, x, add) : false;
@@ -362,7 +488,8 @@ __device__ bool rewrite_word_warp(const TrainState& S, uint32_t w, uint32_t off,
 // warps rewrite the hits.  Rewritten words are appended to the posting pool through the global cursor.
 // Hits of the filter stage, handed from threads to warps through shared memory.
 struct Queue {
-    uint32_t w[QUEUE_CAP], off[QUEUE_CAP], len[QUEUE_CAP];
+    uint32_t w[QUEUE_CAP], off[QUEUE_CAP];
+    unsigned short len[QUEUE_CAP];  // 0xFFFF = long word: the rewriter reads the length again
     unsigned int n;
 };
 
@@ -381,7 +508,7 @@ __device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t 
             if (list) { const uint2 e = __ldcg(list + i); w = e.x; off = e.y; } else { w = i; off = S.w_off[i]; }
             if (word_has_pair(S, w, off, cmd.a, cmd.b, &len)) {
                 unsigned int q = atomicAdd(&Q.n, 1u);
-                if (q < QUEUE_CAP) { Q.w[q] = w; Q.off[q] = off; Q.len[q] = len; }
+                if (q < QUEUE_CAP) { Q.w[q] = w; Q.off[q] = off; Q.len[q] = (unsigned short)min(len, 0xFFFFu); }
                 else if (rewrite_word_serial(S, w, off, len, cmd.a, cmd.b, cmd.x, add)) {
                     unsigned int at = atomicAdd(&S.ctrl->wl_cursor, 1u);
                     if (at < S.wl_cap) S.wl_pool[at] = make_uint2(w, off); else set_status(S.status, ST_LIST_FULL);
@@ -401,7 +528,7 @@ __device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t 
 }
 
 template <bool CLUSTER, int NT>
-__global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
+__global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
     // Driver <-> helper hand-over around a heavy step.  CLUSTER: the hardware cluster barrier on both sides.  Otherwise
     // (a cooperative grid, one CTA per SM): helpers poll a counter in global memory, so the driver's light steps involve
     // no barrier at all and a heavy step has all 148 SMs.
@@ -444,20 +571,24 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         }
     };
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    HotCache& H = *reinterpret_cast<HotCache*>(smem_raw);  // used by the driver CTA only
+    DriverShared& DS = *reinterpret_cast<DriverShared*>(smem_raw);  // used by the driver CTA only
+    HotCache& H = DS.H;
+    NewPairs& NP = DS.NP;
+    Deferred& DQ = DS.DQ;
+    uint32_t* sh_tie = DS.tie;
+    unsigned int* sh_sub = DS.sub;
     __shared__ long long sh_wmax[NT / 32];
-    __shared__ uint32_t sh_tie[MAX_TIES];
     __shared__ unsigned int sh_ntie;
     __shared__ Best sh_win;
     __shared__ Best sh_bestw[NT / 32];
     __shared__ Queue Q;
     __shared__ unsigned int sh_hist[64];
-    __shared__ unsigned int sh_sub[SUB_BINS];
     __shared__ long long sh_T;
     __shared__ int sh_bit;
     __shared__ unsigned int sh_above;
     __shared__ Command sh_cmd;
     __shared__ bool sh_stop;
+    __shared__ unsigned long long sh_px;  // prefix key of the step's new token
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_words = S.ctrl->n_words;
 
@@ -494,6 +625,17 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
     unsigned long long t_start;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_start));
     uint32_t passes = 0;
+    const bool legacy_adders = (S.flags & 8u) != 0;  // experiments: every light step through CacheAdder, as before
+    const bool beats = (S.flags & 16u) != 0;         // debugging: heartbeat (iteration, phase) in pinned host memory on every step;
+                                                     // otherwise only with the watchdog check — a store over PCIe per phase is not free
+    constexpr int PEND = (int)((NPS + NT - 1) / NT);  // new-pair slots per thread when a light step closes
+    int pend_e[PEND];                   // cache entries whose prefix key this thread has asked global memory for
+    unsigned long long pend_v[PEND];
+#pragma unroll
+    for (int r = 0; r < PEND; r++) { pend_e[r] = -1; pend_v[r] = 0; }
+    for (uint32_t k = tid; k < NPS; k += NT) { NP.key[k] = 0; NP.cnt[k] = 0; }
+    if (tid == 0) { NP.overflow = 0; DQ.n = 0; }
+    __syncthreads();
     while (next_id < S.vocab_size) {
         if ((++passes & 255u) == 0) {  // watchdog: a bug must not hang the GPU (default 120 s, far beyond any real training)
             if (tid == 0) {            // one thread decides, so that the whole CTA leaves together
@@ -501,6 +643,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
                 asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
                 sh_stop = now - t_start > (unsigned long long)S.watchdog_s * 1000000000ull && now - t_start < (1ull << 62);
                 if (sh_stop) { set_status(S.status, ST_WATCHDOG); S.ctrl->dbg[4] = iter; S.ctrl->dbg[5] = passes; }
+                S.beat[0] = iter; S.beat[1] = 3;
             }
             __syncthreads();
             if (sh_stop) break;
@@ -508,10 +651,13 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         // Cache invariant: every pair with count >= T has an entry (pairs are appended when their count rises past T;
         // leftovers below T and holes are allowed).  If the best entry has count >= T it is the global argmax;
         // otherwise T is lowered and the cache rebuilt from a log2 histogram of all counts.
-        if (tid == 0) { S.beat[0] = iter; S.beat[1] = need_rebuild ? 1 : 2; }
+        if (beats && tid == 0) { S.beat[0] = iter; S.beat[1] = need_rebuild ? 1 : 2; }
         if (need_rebuild && use_cache) {
             if (++spins > 64) { if (tid == 0) set_status(S.status, ST_PAIR_TABLE_FULL); break; }
-            __syncthreads();  // every thread has read H.n / the winner that sent it here before the cache is wiped
+#pragma unroll
+            for (int r = 0; r < PEND; r++) pend_e[r] = -1;  // the entries they belong to are about to be wiped
+            deferred_drain<NT>(S, H, DQ);  // the rebuild reads global counts: queued updates first (ends with a barrier:
+                                           // every thread has read H.n / the winner that sent it here before the cache is wiped)
             if (tid < 64) sh_hist[tid] = 0;
             for (uint32_t k = tid; k < HIDX; k += NT) H.index[k] = 0;
             if (tid == 0) H.n = 0;
@@ -558,7 +704,10 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             for (uint32_t i = tid; use_cache && i < n_all; i += NT) {
                 uint32_t slot = __ldcg(S.live + i);
                 long long cnt = __ldcg(S.ph_cnt + slot);
-                if (cnt >= T) hc_append(H, __ldcg(S.ph_key + slot), slot, cnt);
+                if (cnt >= T) {
+                    const unsigned long long key = __ldcg(S.ph_key + slot);
+                    hc_append(H, key, slot, cnt, __ldcg(S.tk_pre + (uint32_t)((key - 1) >> 32)));
+                }
             }
             __syncthreads();
             need_rebuild = false;
@@ -566,6 +715,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         if (!use_cache) T = LLONG_MAX;  // GlobalAdder never reports crossings
 
         if ((S.flags & 2u) && use_cache) {  // self-check (experiments): the cache against the global table
+            deferred_drain<NT>(S, H, DQ);
             const uint32_t n_c = min(H.n, HC);
             for (uint32_t i = tid; i < n_c; i += NT)
                 if (H.key[i] && H.cnt[i] != __ldcg(S.ph_cnt + H.slot[i])) {
@@ -574,7 +724,7 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             const uint32_t n_all = __ldcg(&S.ctrl->n_live);
             for (uint32_t i = tid; i < n_all; i += NT) {
                 uint32_t slot = __ldcg(S.live + i);
-                if (__ldcg(S.ph_cnt + slot) >= T && hc_find(H, __ldcg(S.ph_key + slot)) < 0) {
+                if (H.n <= HC && __ldcg(S.ph_cnt + slot) >= T && hc_find(H, __ldcg(S.ph_key + slot)) < 0) {
                     if (atomicAdd(&S.ctrl->dbg[2], 1u) == 0) S.ctrl->dbg[3] = iter;
                 }
             }
@@ -590,21 +740,29 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         if (n_cached > HC) { need_rebuild = true; continue; }  // overflowed: compact (holes, leftovers) or raise T
         const uint32_t n_scan = use_cache ? n_cached : __ldcg(&S.ctrl->n_live);
         long long my_max = 0;
-        if (use_cache) {
-            for (uint32_t i = tid; i < n_scan; i += NT) if (H.key[i]) my_max = max(my_max, H.cnt[i]);
+        if (use_cache) {  // holes and retired entries carry a negative count: no need to look at the keys
+            for (uint32_t i = tid; i < n_scan; i += NT) my_max = max(my_max, H.cnt[i]);
         } else {
             for (uint32_t i = tid; i < n_scan; i += NT) my_max = max(my_max, __ldcg(S.ph_cnt + __ldcg(S.live + i)));
         }
+        const long long my_own = my_max;
+        long long a1 = 0, a2 = 0, a3 = 0, a4 = 0;
+        if (tracer) a1 = clock64();
         for (int o = 16; o; o >>= 1) my_max = max(my_max, __shfl_xor_sync(0xFFFFFFFFu, my_max, o));
         if (lane == 0) sh_wmax[warp] = my_max;
         if (tid == 0) sh_ntie = 0;
+        // Prefix keys requested when the previous step closed have had the scan to arrive.
+#pragma unroll
+        for (int r = 0; r < PEND; r++)
+            if (pend_e[r] >= 0) { H.pre[pend_e[r]] = pend_v[r]; pend_e[r] = -1; }
         __syncthreads();
+        if (tracer) a2 = clock64();
         long long top = lane < NT / 32 ? sh_wmax[lane] : 0;  // every warp folds the per-warp maxima itself: no second barrier
         for (int o = 16; o; o >>= 1) top = max(top, __shfl_xor_sync(0xFFFFFFFFu, top, o));
-        if (top > 0) {
+        if (top > 0 && my_own == top) {  // only a thread that saw the top count looks again, for the entries that have it
             if (use_cache) {
                 for (uint32_t i = tid; i < n_scan; i += NT)
-                    if (H.key[i] && H.cnt[i] == top) { uint32_t k = atomicAdd(&sh_ntie, 1u); if (k < MAX_TIES) sh_tie[k] = i; }
+                    if (H.cnt[i] == top) { uint32_t k = atomicAdd(&sh_ntie, 1u); if (k < MAX_TIES) sh_tie[k] = i; }
             } else {
                 for (uint32_t i = tid; i < n_scan; i += NT) {
                     const uint32_t slot = __ldcg(S.live + i);
@@ -612,7 +770,10 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
                 }
             }
         }
+        if (tracer) a3 = clock64();
         __syncthreads();
+        if (tracer) a4 = clock64();
+        Best win{0, 0, 0};
         if (top > 0 && sh_ntie > MAX_TIES) {
             // very many pairs tie at the top (late in a small corpus): the general reduction, restricted to the tied entries
             Best best{0, 0, 0};
@@ -637,25 +798,44 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
                 }
                 if (lane == 0) sh_win = bb;
             }
-        } else if (warp == 0) {  // the tied entries (usually one): order by bytes
+            __syncthreads();
+            win = sh_win;
+        } else {  // the tied entries (usually one): order by bytes.  Every warp does it for itself: no hand-over, no barrier.
             const uint32_t n_tie = top > 0 ? sh_ntie : 0;
             Best bb{0, 0, 0};
-            for (uint32_t k = lane; k < n_tie; k += 32) {
-                const uint32_t e = sh_tie[k];
-                Best c{top, use_cache ? H.key[e] : __ldcg(S.ph_key + e), e};
-                if (bb.cnt == 0 || better(S, c, bb)) bb = c;
-            }
-            if (n_tie > 1) {
+            // equal counts: order by (bytes(a), bytes(b)).  With the cache, different first tokens whose prefix keys
+            // differ are ordered from shared memory; anything else falls back to the token bytes in global memory.
+            auto wins = [&](const Best& c, const Best& d) -> bool {  // c before d ?
+                if (use_cache && (c.key >> 32) != (d.key >> 32)) {  // key - 1 cannot carry into the high word for b < 2^32 - 1
+                    const unsigned long long pc = H.pre[c.slot], pd = H.pre[d.slot];
+                    if (pc != PRE_UNKNOWN && pd != PRE_UNKNOWN && pc != pd) return pc > pd;
+                }
+                return better(S, c, d);
+            };
+            if (n_tie == 1) {
+                const uint32_t e = sh_tie[0];
+                bb = Best{top, use_cache ? H.key[e] : __ldcg(S.ph_key + e), e};
+            } else if (n_tie > 1) {
+                for (uint32_t k = lane; k < n_tie; k += 32) {
+                    const uint32_t e = sh_tie[k];
+                    Best c{top, use_cache ? H.key[e] : __ldcg(S.ph_key + e), e};
+                    if (bb.cnt == 0 || wins(c, bb)) bb = c;
+                }
                 for (int o = 16; o; o >>= 1) {
                     Best other = shfl_best(bb, o, false);
-                    if (other.cnt > 0 && (bb.cnt == 0 || better(S, other, bb))) bb = other;
+                    if (other.cnt > 0 && (bb.cnt == 0 || wins(other, bb))) bb = other;
                 }
+                bb.cnt = __shfl_sync(0xFFFFFFFFu, bb.cnt, 0); bb.key = __shfl_sync(0xFFFFFFFFu, bb.key, 0); bb.slot = __shfl_sync(0xFFFFFFFFu, bb.slot, 0);
             }
-            if (lane == 0) sh_win = bb;
+            win = bb;
+            if (tracer) S.ctrl->sub_clk[6] += n_tie;
         }
-        __syncthreads();
-        if (tracer) c1 = clock64();
-        const Best win = sh_win;  // .slot = index of the cache entry (global slot without the cache)
+        if (tracer) {
+            c1 = clock64();
+            S.ctrl->sub_clk[0] += a1 - c0; S.ctrl->sub_clk[1] += a2 - a1; S.ctrl->sub_clk[2] += a3 - a2; S.ctrl->sub_clk[3] += a4 - a3;
+            S.ctrl->sub_clk[4] += c1 - a4; S.ctrl->sub_clk[5] += n_scan;
+        }
+        // win.slot = index of the cache entry (global slot without the cache)
         if (!use_cache) {
             if (win.cnt <= 0) break;  // nothing qualifies (bpe_trainer.py:242: heap exhausted)
         } else if (win.cnt < T) {     // the best cached pair is below the threshold: pairs outside the cache may beat it
@@ -680,40 +860,90 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         const uint32_t first_new_entry = n_cached;
         uint32_t matched = 0;
         if (tid == 0) Q.n = 0;
-        if (leader) {  // bookkeeping for x beside the rewrite (speculative: overwritten if the step merges nothing)
+        if (warp == NT / 32 - 1) {  // bookkeeping for x beside the rewrite (speculative: overwritten if the step merges nothing)
+            // The last warp copies the bytes of a and b behind one another, a lane per byte: all loads are in flight together
+            // (a one-thread loop would pay a round trip to L2 per byte, and the whole CTA waits for it at the next barrier).
             const uint32_t oa = __ldcg(S.tk_off + a), ob = __ldcg(S.tk_off + b), o = __ldcg(S.tk_off + x);
             const uint32_t la = __ldcg(S.tk_off + a + 1) - oa, lb = __ldcg(S.tk_off + b + 1) - ob;
-            unsigned long long px = 0;
+            uint32_t px_hi = 0, px_lo = 0;
             if (o + la + lb <= S.blob_cap) {
-                for (uint32_t i = 0; i < la + lb; i++) {
-                    uint8_t v = i < la ? S.tk_blob[oa + i] : S.tk_blob[ob + i - la];
-                    S.tk_blob[o + i] = v;
-                    if (i < 8) px |= (unsigned long long)v << (56 - 8 * i);
+                for (uint32_t i0 = 0; i0 < la + lb; i0 += 32) {
+                    const uint32_t i = i0 + lane;
+                    if (i < la + lb) {
+                        const uint32_t v = i < la ? __ldcg(S.tk_blob + oa + i) : __ldcg(S.tk_blob + ob + i - la);
+                        S.tk_blob[o + i] = (uint8_t)v;
+                        if (i < 4) px_hi = v << (24 - 8 * i);
+                        else if (i < 8) px_lo = v << (56 - 8 * i);
+                    }
                 }
-            } else set_status(S.status, ST_LIST_FULL);
-            S.tk_off[x + 1] = o + la + lb;
-            S.tk_pre[x] = px;
-            S.m_a[x - S.first_new_id] = a; S.m_b[x - S.first_new_id] = b;
-            S.wl_off[x] = wl_start;
+            } else if (lane == 0) set_status(S.status, ST_LIST_FULL);
+            px_hi = __reduce_or_sync(0xFFFFFFFFu, px_hi);
+            px_lo = __reduce_or_sync(0xFFFFFFFFu, px_lo);
+            if (lane == 0) {
+                S.tk_off[x + 1] = o + la + lb;
+                S.tk_pre[x] = ((unsigned long long)px_hi << 32) | px_lo;
+                sh_px = ((unsigned long long)px_hi << 32) | px_lo;
+                S.m_a[x - S.first_new_id] = a; S.m_b[x - S.first_new_id] = b;
+                S.wl_off[x] = wl_start;
+            }
         }
         if (tracer) c2 = clock64();
         if (list_tok != NONE && list_len <= LIGHT_MAX) {
             // light step, this CTA alone: filter (one thread per posting), then one warp per hit
             const uint2* list = S.wl_pool + list_off;
-            __syncthreads();  // Q.n = 0
-            for (uint32_t i = tid; i < list_len; i += NT) {
-                const uint2 e = __ldcg(list + i);
-                uint32_t len;
-                if (word_has_pair(S, e.x, e.y, a, b, &len)) {  // list_len <= QUEUE_CAP
-                    const unsigned int q = atomicAdd(&Q.n, 1u);
-                    Q.w[q] = e.x; Q.off[q] = e.y; Q.len[q] = len;
-                }
+            const bool light_adders = use_cache && !legacy_adders;
+            // The updates deferred by the previous step: the first compare-and-swap of each is issued here, in front of
+            // the posting loads, and looked at behind the filter — its round trip disappears behind theirs.
+            const unsigned int dq_n = min(DQ.n, DQ_CAP);
+            unsigned long long dq_key = 0, dq_cur = 0;
+            uint64_t dq_slot = 0;
+            if (tid < dq_n) {
+                dq_key = DQ.key[tid];
+                dq_slot = (dq_key * 0x9E3779B97F4A7C15ull >> 20) & S.ph_mask;
+                dq_cur = atomicCAS(S.ph_key + dq_slot, 0ull, dq_key);
             }
+            __syncthreads();  // Q.n = 0; every thread has read DQ.n
+            if (tid == 0) DQ.n = 0;  // nothing is queued between the two barriers around the filter; the items stay readable
+            // Four postings per thread and pass: the posting loads of a pass are in flight together, then the symbol
+            // loads — a list of up to 4 * NT words costs two round trips, not eight.
+            for (uint32_t i0 = tid; i0 < list_len; i0 += 4 * NT) {
+                uint2 e[4];
+                uint4 v[4];
+                uint32_t len[4];
+#pragma unroll
+                for (int r = 0; r < 4; r++)
+                    if (i0 + r * NT < list_len) e[r] = __ldcg(list + i0 + r * NT);
+#pragma unroll
+                for (int r = 0; r < 4; r++)
+                    if (i0 + r * NT < list_len) {
+                        v[r] = __ldcg(reinterpret_cast<const uint4*>(S.sym + e[r].y));
+                        len[r] = __ldcg(S.w_len + e[r].x);
+                    }
+#pragma unroll
+                for (int r = 0; r < 4; r++)
+                    if (i0 + r * NT < list_len && word_has_pair_loaded(S, e[r].y, v[r], len[r], a, b)) {  // list_len <= QUEUE_CAP
+                        const unsigned int q = atomicAdd(&Q.n, 1u);
+                        Q.w[q] = e[r].x; Q.off[q] = e[r].y; Q.len[q] = (unsigned short)min(len[r], 0xFFFFu);
+                    }
+            }
+            if (tid < dq_n) {
+                const unsigned short entry = DQ.entry[tid];
+                unsigned long long pre = PRE_UNKNOWN;
+                const bool want_pre = entry != 0xFFFFu && H.pre[entry] == PRE_UNKNOWN;
+                if (want_pre) pre = __ldcg(S.tk_pre + (uint32_t)((dq_key - 1) >> 32));
+                const uint64_t slot = pair_slot_resume(S, dq_key, dq_slot, dq_cur);
+                global_add(S, slot, DQ.delta[tid]);
+                if (entry != 0xFFFFu) { H.slot[entry] = (uint32_t)slot; if (want_pre) H.pre[entry] = pre; }
+            }
+            for (unsigned int i = tid + NT; i < dq_n; i += NT) deferred_apply(S, H, DQ.key[i], DQ.delta[i], DQ.entry[i]);
             __syncthreads();
             matched = Q.n;
-            if (tid == 0) S.beat[1] = 5;
+            if (beats && tid == 0) S.beat[1] = 5;
             if (tracer) c3 = clock64();
-            if (use_cache) {
+            if (light_adders) {
+                const LightAdder add{S, H, NP, DQ, T, x};
+                for (uint32_t k = warp; k < matched; k += NT / 32) rewrite_word_warp(S, Q.w[k], Q.off[k], Q.len[k], a, b, x, add);
+            } else if (use_cache) {
                 const CacheAdder add{S, H, T};
                 for (uint32_t k = warp; k < matched; k += NT / 32) rewrite_word_warp(S, Q.w[k], Q.off[k], Q.len[k], a, b, x, add);
             } else {
@@ -723,30 +953,68 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             for (uint32_t k = tid; k < matched; k += NT) {  // the hits ARE x's posting list
                 if (wl_start + k < S.wl_cap) S.wl_pool[wl_start + k] = make_uint2(Q.w[k], Q.off[k]); else set_status(S.status, ST_LIST_FULL);
             }
-            if (tid == 0) S.beat[1] = 6;
-            __threadfence();  // the count updates were posted without waiting: they must have landed before the reload below
-            __syncthreads();
-            // entries appended during this step: their count comes from the (exact) global table
-            const uint32_t n_now = use_cache ? min(H.n, HC) : 0;
-            for (uint32_t i = first_new_entry + tid; i < n_now; i += NT)
-                if (H.key[i]) H.cnt[i] = __ldcg(S.ph_cnt + H.slot[i]);
+            if (beats && tid == 0) S.beat[1] = 6;
+            if (light_adders) {
+                __syncthreads();
+                // Close the step's new pairs: exact counts, straight from shared memory.
+                const uint32_t n_after = min(H.n, HC);  // beyond first_new_entry: appended by the CacheAdder fallback, if any
+                const bool fell_back = NP.overflow != 0;
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < PEND; r++) {
+                    const uint32_t k = tid + r * NT;
+                    pend_e[r] = -1;
+                    if (k >= NPS) continue;
+                    const uint32_t code = NP.key[k];
+                    if (!code) continue;
+                    const long long c = NP.cnt[k];
+                    NP.key[k] = 0; NP.cnt[k] = 0;
+                    const uint32_t other = (code - 1) >> 1;
+                    const uint32_t pa = ((code - 1) & 1u) ? x : other, pb = ((code - 1) & 1u) ? other : x;
+                    const unsigned long long key = (((unsigned long long)pa << 32) | pb) + 1ull;
+                    int e = -1;
+                    if (c >= T) {
+                        e = hc_append(H, key, 0u, c, pa == x ? sh_px : PRE_UNKNOWN);  // the global slot arrives with the deferred update
+                        if (e >= 0 && pa != x) {  // the prefix key of `other`: asked for now, stored on the way into the next tie-break
+                            pend_e[r] = e;
+                            pend_v[r] = __ldcg(S.tk_pre + other);
+                        }
+                    }
+                    deferred_push(S, H, DQ, key, c, e >= 0 ? (unsigned short)e : (unsigned short)0xFFFFu);
+                }
+                if (fell_back) {  // rare: more distinct new pairs than NewPairs holds; those went the CacheAdder way
+                    __threadfence();
+                    __syncthreads();
+                    for (uint32_t i = first_new_entry + tid; i < n_after; i += NT)
+                        if (H.key[i]) H.cnt[i] = __ldcg(S.ph_cnt + H.slot[i]);
+                    if (tid == 0) NP.overflow = 0;
+                }
+            } else {
+                __threadfence();  // the count updates were posted without waiting: they must have landed before the reload below
+                __syncthreads();
+                // entries appended during this step: their count comes from the (exact) global table
+                const uint32_t n_now = use_cache ? min(H.n, HC) : 0;
+                for (uint32_t i = first_new_entry + tid; i < n_now; i += NT)
+                    if (H.key[i]) H.cnt[i] = __ldcg(S.ph_cnt + H.slot[i]);
+            }
         } else {
             // heavy step: wake the helper CTAs; counts change behind the cache's back, so reload it afterwards
+            deferred_drain<NT>(S, H, DQ);  // queued updates land (and new cache entries learn their slots) before anyone reads global counts
             if (tid == 0) {
                 S.ctrl->wl_cursor = wl_start;
                 S.ctrl->n_hot = 0;
                 S.ctrl->cmd = Command{1u, a, b, x, list_tok, list_len, T};
                 __threadfence();
-                S.beat[1] = 7;
+                if (beats) S.beat[1] = 7;
             }
             driver_wake();
-            if (tid == 0) S.beat[1] = 8;
+            if (beats && tid == 0) S.beat[1] = 8;
             if (tracer) c3 = clock64();
             const Command cmd{1u, a, b, x, list_tok, list_len, T};
             heavy_rewrite<NT>(S, cmd, n_words, Q);
-            if (tid == 0) S.beat[1] = 9;
+            if (beats && tid == 0) S.beat[1] = 9;
             driver_join();
-            if (tid == 0) S.beat[1] = 10;
+            if (beats && tid == 0) S.beat[1] = 10;
             matched = __ldcg(&S.ctrl->wl_cursor) - wl_start;
             for (uint32_t i = tid; i < n_cached; i += NT)
                 if (H.key[i]) H.cnt[i] = __ldcg(S.ph_cnt + H.slot[i]);
@@ -754,13 +1022,14 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
             __syncthreads();
             for (uint32_t i = tid; i < n_pending; i += NT) {
                 const ulonglong2 rec = __ldcg(S.hot + i);
-                if (hc_find(H, rec.x) < 0) hc_append(H, rec.x, (uint32_t)rec.y, __ldcg(S.ph_cnt + (uint32_t)rec.y));
+                if (hc_find(H, rec.x) < 0)
+                    hc_append(H, rec.x, (uint32_t)rec.y, __ldcg(S.ph_cnt + (uint32_t)rec.y), __ldcg(S.tk_pre + (uint32_t)((rec.x - 1) >> 32)));
             }
             n_heavy++;
         }
         if (tracer) c4 = clock64();
         // ---- close the step ---------------------------------------------------------------------------------------------
-        if (tid == 0) S.beat[1] = 11;
+        if (beats && tid == 0) S.beat[1] = 11;
         if (leader) {
             if (use_cache) {
                 H.cnt[win.slot] = RETIRED;                 // the winner never occurs again (bpe_trainer.py:243);
@@ -769,7 +1038,8 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
                 S.ph_cnt[win.slot] = RETIRED;
             }
             if (matched) S.wl_len[x] = matched;
-            __threadfence();
+            // no fence here: this CTA sees the stores after the barrier below, and every hand-over to other CTAs (heavy
+            // step) or re-read of global counts (rebuild) starts with deferred_drain, whose fence covers them
         }
         if (matched) {  // bpe_trainer.py:309-316
             wl_cur = wl_start + matched;
@@ -778,8 +1048,12 @@ __global__ void __launch_bounds__(NT) merge_loop_kernel(TrainState S) {
         __syncthreads();  // cache and leader stores are ordered before the next argmax of this CTA
         if (tracer) {
             long long c5 = clock64();
-            S.ctrl->phase_clk[0] += c1 - c0; S.ctrl->phase_clk[1] += c2 - c1; S.ctrl->phase_clk[2] += c3 - c2;
-            S.ctrl->phase_clk[3] += c4 - c3; S.ctrl->phase_clk[4] += c5 - c4;
+            if (list_tok != NONE && list_len <= LIGHT_MAX) {
+                S.ctrl->phase_clk[0] += c1 - c0; S.ctrl->phase_clk[1] += c2 - c1; S.ctrl->phase_clk[2] += c3 - c2;
+                S.ctrl->phase_clk[3] += c4 - c3; S.ctrl->phase_clk[4] += c5 - c4; S.ctrl->phase_clk[6]++;
+            } else {
+                S.ctrl->phase_clk[5] += c5 - c0; S.ctrl->phase_clk[7]++;
+            }
         }
         if (S.trace && leader && iter < S.vocab_size) {
             unsigned long long now;
@@ -903,10 +1177,10 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     if (mode && !strcmp(mode, "cluster")) {
         auto kern = merge_loop_kernel<true, 1024>;
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HotCache));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DriverShared));
         for (int csize = 16; csize >= 8 && !launched && e == cudaSuccess; csize -= 8) {
             cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = dim3(csize); cfg.blockDim = dim3(1024); cfg.dynamicSmemBytes = sizeof(HotCache); cfg.stream = s;
+            cfg.gridDim = dim3(csize); cfg.blockDim = dim3(1024); cfg.dynamicSmemBytes = sizeof(DriverShared); cfg.stream = s;
             cudaLaunchAttribute attr[1];
             attr[0].id = cudaLaunchAttributeClusterDimension;
             attr[0].val.clusterDim.x = csize; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
@@ -923,8 +1197,8 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
         void (*kern)(TrainState) = nt == 1024 ? merge_loop_kernel<false, 1024> : nt == 256 ? merge_loop_kernel<false, 256> : merge_loop_kernel<false, 512>;
         if (nt != 1024 && nt != 256) nt = 512;
         int per_sm = 0;
-        CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HotCache)));
-        CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt, sizeof(HotCache)));
+        CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DriverShared)));
+        CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt, sizeof(DriverShared)));
         cudaDeviceProp prop;
         CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, ctx->device));
         int grid = per_sm >= 1 ? prop.multiProcessorCount : 1;  // helpers poll a flag: every CTA must be resident (cooperative launch)
@@ -934,7 +1208,7 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
         }
         KernelTimer t(ctx, "merge_loop_kernel", s);
         void* args[] = {&S};
-        CUDA_TRY(ctx, cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(nt), args, sizeof(HotCache), s));
+        CUDA_TRY(ctx, cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(nt), args, sizeof(DriverShared), s));
         launched_ctas = grid;
     }
     {   // wait with a deadline
@@ -971,9 +1245,14 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
         fprintf(stderr, "[train check] stale cache copies %u (first at iteration %u), hot pairs missing from the cache %u (first at iteration %u), rebuilds %u, heavy %u, iterations %u\n",
                 h_ctrl.dbg[0], h_ctrl.dbg[1], h_ctrl.dbg[2], h_ctrl.dbg[3], h_ctrl.n_rebuilds, h_ctrl.n_heavy, h_ctrl.n_iters);
     if (trace_path) {  // developer aid: per-iteration timings of the loop
-        fprintf(stderr, "[train trace] driver thread 0 cycles: argmax %llu, select+bookkeeping %llu, filter/wake %llu, rewrite %llu, close %llu; "
-                        "rebuilds %u, heavy steps %u\n", h_ctrl.phase_clk[0], h_ctrl.phase_clk[1], h_ctrl.phase_clk[2], h_ctrl.phase_clk[3],
-                h_ctrl.phase_clk[4], h_ctrl.n_rebuilds, h_ctrl.n_heavy);
+        const double nl = (double)std::max<unsigned long long>(1, h_ctrl.phase_clk[6]), nh = (double)std::max<unsigned long long>(1, h_ctrl.phase_clk[7]);
+        fprintf(stderr, "[train trace] driver thread 0, SM cycles per LIGHT step (%llu steps): argmax %.0f, select+bookkeeping %.0f, filter %.0f, rewrite %.0f, "
+                        "close %.0f; per HEAVY step (%llu steps): %.0f; rebuilds %u\n", h_ctrl.phase_clk[6], h_ctrl.phase_clk[0] / nl, h_ctrl.phase_clk[1] / nl,
+                h_ctrl.phase_clk[2] / nl, h_ctrl.phase_clk[3] / nl, h_ctrl.phase_clk[4] / nl, h_ctrl.phase_clk[7], h_ctrl.phase_clk[5] / nh, h_ctrl.n_rebuilds);
+        const double ni = (double)std::max(1u, h_ctrl.n_iters);
+        fprintf(stderr, "[train trace] argmax, cycles per step: scan %.0f, reduce+barrier %.0f, ties %.0f, barrier %.0f, order %.0f (candidates %.2f); entries scanned %.0f\n",
+                h_ctrl.sub_clk[0] / ni, h_ctrl.sub_clk[1] / ni, h_ctrl.sub_clk[2] / ni, h_ctrl.sub_clk[3] / ni, h_ctrl.sub_clk[4] / ni,
+                h_ctrl.sub_clk[6] / ni, h_ctrl.sub_clk[5] / ni);
         std::vector<uint32_t> tr(4ull * h_ctrl.n_iters);
         cudaMemcpy(tr.data(), d_trace, tr.size() * 4, cudaMemcpyDeviceToHost);
         if (FILE* f = fopen(trace_path, "w")) {
