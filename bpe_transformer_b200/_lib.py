@@ -9,6 +9,7 @@ import ctypes as C
 import os
 import pathlib
 import threading
+import time
 import warnings
 
 import numpy as np
@@ -25,7 +26,7 @@ SYMBOLS = [
     "bpe_ctx_create", "bpe_ctx_destroy", "bpe_last_error", "bpe_ctx_configure", "bpe_set_special_tokens", "bpe_scan",
     "bpe_count", "bpe_unique_stats", "bpe_unique_export", "bpe_unique_import", "bpe_unique_reset", "bpe_train",
     "bpe_train_timing", "bpe_load_model", "bpe_encode", "bpe_decode", "bpe_kernel_times", "bpe_set_profiling",
-    "bpe_decode_noalloc", "bpe_load_file", "bpe_store_to_host",
+    "bpe_decode_noalloc", "bpe_load_file", "bpe_store_to_host", "bpe_load_file_ranges",
 ]
 
 
@@ -81,6 +82,7 @@ def load_library():
                                            C.c_char_p, C.c_size_t]
         lib.bpe_load_file.argtypes = [vp, C.c_char_p, C.c_uint64, C.c_uint64, u8p, vp]
         lib.bpe_store_to_host.argtypes = [vp, vp, C.c_uint64, vp, vp]
+        lib.bpe_load_file_ranges.argtypes = [vp, C.c_char_p, C.c_uint32, u64p, u64p, u64p, u8p, C.POINTER(C.c_uint64), vp]
         lib.bpe_kernel_times.argtypes = [vp, C.POINTER(KernelTime), C.c_int]
         lib.bpe_set_profiling.argtypes = [vp, C.c_int]
         for name in SYMBOLS:
@@ -196,6 +198,11 @@ class Engine:
         if n:
             self._check(self.lib.bpe_load_file(self.ctx, os.fsencode(path), lo, n, dev.data_ptr(), self._stream()))
         return dev, n
+
+    def load_file_ranges(self, path, offsets: list[int]) -> "RangeLoad":
+        """Starts loading the byte ranges [offsets[k], offsets[k+1]) of a file on a host thread, each range to its own
+        16-byte aligned, padded place in ONE device buffer.  `RangeLoad.piece(k)` blocks until range k has landed."""
+        return RangeLoad(self, path, offsets)
 
     def to_host_array(self, d_tensor, dtype) -> np.ndarray:
         """Device tensor -> new NumPy array of `dtype` (same bytes), through the pinned staging buffers."""
@@ -324,6 +331,62 @@ class Engine:
         out = torch.empty(n_bytes.value + 16, dtype=torch.uint8, device=f"cuda:{self.device}")
         self._check(self.lib.bpe_decode(*args, out.data_ptr(), n_bytes.value, C.byref(n_bytes), self._stream()))
         return out[:n_bytes.value]
+
+
+class RangeLoad:
+    """A running bpe_load_file_ranges call (one host thread) and the device buffer it fills."""
+
+    def __init__(self, engine: Engine, path, offsets: list[int]):
+        torch = engine.torch
+        self.engine = engine
+        lens = [b - a for a, b in zip(offsets[:-1], offsets[1:])]
+        self.lens = lens
+        dev_off, at = [], 0
+        for n in lens:
+            dev_off.append(at)
+            at = (at + n + TEXT_PAD + 15) & ~15  # every piece: 16-byte aligned start, TEXT_PAD readable bytes behind it
+        self.dev_off = dev_off
+        self.buffer = torch.empty(at + TEXT_PAD, dtype=torch.uint8, device=f"cuda:{engine.device}")
+        self._file_off = np.asarray(offsets[:-1], dtype=np.uint64)
+        self._len = np.asarray(lens, dtype=np.uint64)
+        self._dev_off = np.asarray(dev_off, dtype=np.uint64)
+        self._done = C.c_uint64(0)
+        self._rc: int | None = None
+        self._error: BaseException | None = None
+        self._path = os.fsencode(path)
+        self._stream = engine._stream()
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
+
+    def _run(self):
+        try:
+            self.engine.torch.cuda.set_device(self.engine.device)
+            self._rc = self.engine.lib.bpe_load_file_ranges(self.engine.ctx, self._path, len(self.lens), _np_ptr(self._file_off), _np_ptr(self._len),
+                                                            _np_ptr(self._dev_off), self.buffer.data_ptr(), C.byref(self._done), self._stream)
+        except BaseException as e:  # noqa: BLE001 - re-raised by piece() / join()
+            self._error = e
+
+    def _check(self):
+        if self._error is not None:
+            raise self._error
+        if self._rc:
+            self.engine._check(self._rc)
+
+    def piece(self, k: int):
+        """(device tensor view, length) of range k, once it is completely in device memory."""
+        while self._done.value <= k:
+            if not self._thread.is_alive():
+                self._check()
+                if self._done.value <= k:
+                    raise RuntimeError("bpe_load_file_ranges ended before the range arrived")
+                break
+            time.sleep(0.0001)
+        a, n = self.dev_off[k], self.lens[k]
+        return self.buffer[a:a + n + TEXT_PAD], n
+
+    def join(self):
+        self._thread.join()
+        self._check()
 
 
 def host_array(n_items: int, dtype) -> np.ndarray:

@@ -12,6 +12,7 @@
 #include <atomic>
 #include <condition_variable>
 #include <functional>
+#include <memory>
 #include <mutex>
 #include <cstdlib>
 #include <cstring>
@@ -181,6 +182,79 @@ extern "C" int bpe_load_file(bpe_ctx* ctx, const char* path, uint64_t offset, ui
     });
     close(fd);
     (void)stream;  // the copy has completed on return: any stream may read the buffer afterwards
+    if (rc == 1) return ctx_fail(ctx, BPE_ERR_ARGUMENT, "short read");
+    if (rc) return ctx_fail(ctx, BPE_ERR_CUDA, "host-to-device copy", cudaGetLastError());
+    return BPE_OK;
+}
+
+// Several byte ranges of one file, each to its own place in a device buffer, in one pass of the lanes; *h_ranges_done
+// (ordinary host memory, polled by the caller from another thread) counts the leading ranges that have landed completely.
+extern "C" int bpe_load_file_ranges(bpe_ctx* ctx, const char* path, uint32_t n_ranges, const uint64_t* file_off, const uint64_t* len,
+                                    const uint64_t* dev_off, uint8_t* d_base, volatile uint64_t* h_ranges_done, void* stream) {
+    if (!ctx || !path || (n_ranges && (!file_off || !len || !dev_off || !d_base)))
+        return ctx ? ctx_fail(ctx, BPE_ERR_ARGUMENT, "bpe_load_file_ranges arguments") : BPE_ERR_ARGUMENT;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (h_ranges_done) *h_ranges_done = 0;
+    Staging* st = staging_of(ctx, 0);
+    if (!st) return BPE_ERR_CUDA;
+    struct Chunk { uint64_t file_off, dev_off; uint32_t len, range; };
+    std::vector<Chunk> chunks;
+    std::vector<uint64_t> range_end(n_ranges);  // chunks [0, range_end[r]) cover ranges 0..r
+    for (uint32_t r = 0; r < n_ranges; r++) {
+        for (uint64_t o = 0; o < len[r]; o += kLaneBytes)
+            chunks.push_back(Chunk{file_off[r] + o, dev_off[r] + o, (uint32_t)std::min<uint64_t>(kLaneBytes, len[r] - o), r});
+        range_end[r] = chunks.size();
+    }
+    const uint64_t n_chunks = chunks.size();
+    auto publish = [&](uint64_t landed_chunks) {
+        if (!h_ranges_done) return;
+        uint64_t r = *h_ranges_done;
+        while (r < n_ranges && range_end[r] <= landed_chunks) r++;
+        __atomic_store_n(const_cast<uint64_t*>(h_ranges_done), r, __ATOMIC_RELEASE);
+    };
+    if (n_chunks == 0) { publish(0); return BPE_OK; }
+    int fd = open(path, O_RDONLY);
+    if (fd < 0) return ctx_fail(ctx, BPE_ERR_ARGUMENT, "cannot open file");
+    std::unique_ptr<std::atomic<uint8_t>[]> landed(new std::atomic<uint8_t>[n_chunks]);
+    for (uint64_t c = 0; c < n_chunks; c++) landed[c].store(0, std::memory_order_relaxed);
+    std::mutex mark_mu;
+    uint64_t watermark = 0;  // chunks [0, watermark) are in device memory
+    auto mark = [&](uint64_t c) {
+        landed[c].store(1, std::memory_order_release);
+        std::lock_guard<std::mutex> lock(mark_mu);
+        const uint64_t before = watermark;
+        while (watermark < n_chunks && landed[watermark].load(std::memory_order_acquire)) watermark++;
+        if (watermark != before) publish(watermark);
+    };
+    std::atomic<uint64_t> next{0};
+    int rc = st->run(n_chunks, [&](int lane) -> int {
+        int bad = 0;
+        uint64_t in_flight[2] = {~0ull, ~0ull};  // chunk copied from buffer b and not yet known to have landed
+        for (int it = 0;; it++) {
+            const uint64_t c = next.fetch_add(1);
+            if (c >= n_chunks) break;
+            const int b = it & 1;
+            const Chunk& ch = chunks[c];
+            if (in_flight[b] != ~0ull) {
+                if (cudaEventSynchronize(st->done[lane][b]) != cudaSuccess) { bad = 2; break; }
+                mark(in_flight[b]);
+                in_flight[b] = ~0ull;
+            }
+            if (!pread_all(fd, st->buf(lane, b), ch.len, ch.file_off)) { bad = 1; break; }
+            if (cudaMemcpyAsync(d_base + ch.dev_off, st->buf(lane, b), ch.len, cudaMemcpyHostToDevice, st->copy[lane]) != cudaSuccess ||
+                cudaEventRecord(st->done[lane][b], st->copy[lane]) != cudaSuccess) { bad = 2; break; }
+            in_flight[b] = c;
+            // the copy issued one round ago has had a whole pread to finish: report it now rather than a round later
+            if (in_flight[b ^ 1] != ~0ull && cudaEventQuery(st->done[lane][b ^ 1]) == cudaSuccess) { mark(in_flight[b ^ 1]); in_flight[b ^ 1] = ~0ull; }
+        }
+        if (cudaStreamSynchronize(st->copy[lane]) != cudaSuccess && !bad) bad = 2;
+        if (!bad)
+            for (int b = 0; b < 2; b++)
+                if (in_flight[b] != ~0ull) mark(in_flight[b]);
+        return bad;
+    });
+    close(fd);
+    (void)stream;
     if (rc == 1) return ctx_fail(ctx, BPE_ERR_ARGUMENT, "short read");
     if (rc) return ctx_fail(ctx, BPE_ERR_CUDA, "host-to-device copy", cudaGetLastError());
     return BPE_OK;

@@ -1066,6 +1066,9 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
     }
     if (tid == 0) {
         S.ctrl->n_iters = iter; S.ctrl->n_merges = next_id - S.first_new_id; S.ctrl->n_heavy = n_heavy;
+        unsigned int smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        S.ctrl->dbg[7] = smid;
         S.ctrl->cmd.op = 0;
         __threadfence();
         S.beat[1] = 12;
@@ -1264,6 +1267,9 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     cudaEventElapsedTime(&ms0, ev[0], ev[1]);
     cudaEventElapsedTime(&ms1, ev[1], ev[2]);
     ctx->train_ms[0] = ms0; ctx->train_ms[1] = ms1; ctx->train_ms[2] = h_ctrl.n_iters;
+    if (getenv("BPE_B200_TRAIN_VERBOSE"))
+        fprintf(stderr, "[bpe_train] merge loop %.2f ms, %u iterations, %u heavy steps, %u rebuilds, driver CTA on SM %u\n", ms1, h_ctrl.n_iters,
+                h_ctrl.n_heavy, h_ctrl.n_rebuilds, h_ctrl.dbg[7]);
     for (auto& e : ev) cudaEventDestroy(e);
     return ctx_status_to_code(ctx, ctx_read_status(ctx, s));
 }

@@ -23,7 +23,7 @@ from ... import _lib
 from ...settings import ENCODING_STD
 
 
-_PIPE_BYTES = int(os.environ.get("BPE_B200_PIPE_BYTES", str(128 << 20)))  # piece size of the load / count pipeline
+_PIPE_BYTES = int(os.environ.get("BPE_B200_COUNT_PIPE_BYTES", str(256 << 20)))  # piece size of the load / count pipeline
 
 
 # --------------------------------------------------------------------------------------------------------
@@ -153,58 +153,30 @@ def count_into_engine(engine: "_lib.Engine", file_path, special_tokens: list[str
 
 def _count_file_pipelined(engine: "_lib.Engine", file_path, special_tokens: list[str]) -> str:
     """Large corpora with special tokens: pieces cut at special-token starts (the reference's own chunk rule, so the
-    cuts cannot change the result) are read into HBM by a host thread while the GPU scans and counts the piece
-    before.  Returns "counted", or why the caller has to start again: "capacity" / "invalid-utf8"."""
-    import queue
-    import threading
-
-    import torch
-
+    cuts cannot change the result) stream into HBM in one pass of the I/O lanes while the GPU scans and counts the
+    pieces that have landed.  Returns "counted", or why the caller has to start again: "capacity" / "invalid-utf8"."""
     size = os.path.getsize(file_path)
     with open(file_path, "rb") as fh:
         offs = find_chunk_boundaries(fh, max(2, -(-size // _PIPE_BYTES)), special_tokens)
-    loaded: queue.Queue = queue.Queue(maxsize=2)
-    errors: list[BaseException] = []
-    stop = threading.Event()
-
-    def loader():
-        try:
-            torch.cuda.set_device(engine.device)
-            for a, b in zip(offs[:-1], offs[1:]):
-                if stop.is_set():
-                    break
-                loaded.put(engine.load_file(file_path, a, b))
-        except BaseException as e:  # noqa: BLE001 - re-raised on the calling thread
-            errors.append(e)
-        finally:
-            loaded.put(None)
-
-    thread = threading.Thread(target=loader, daemon=True)
-    thread.start()
+    load = engine.load_file_ranges(file_path, offs)  # one pass of the I/O lanes over the whole file, on its own thread
     outcome = "counted"
-    while True:
-        item = loaded.get()
-        if item is None:
-            break
-        if stop.is_set():
-            continue
-        d_text, n = item
+    try:
+        for k in range(len(offs) - 1):
+            d_text, n = load.piece(k)  # blocks until piece k has landed; later pieces keep arriving meanwhile
+            if n:
+                engine.count(d_text, n, engine.scan(d_text, n))
+    except _lib.InvalidUtf8:
+        outcome = "invalid-utf8"
+    except _lib.BpeError as e:
+        if e.code != _lib.ERR_CAPACITY:
+            raise
+        outcome = "capacity"
+    finally:
         try:
-            engine.count(d_text, n, engine.scan(d_text, n))
-        except _lib.InvalidUtf8:
-            outcome = "invalid-utf8"
-            stop.set()
-        except _lib.BpeError as e:
-            if e.code != _lib.ERR_CAPACITY:
-                errors.append(e)
-            outcome = "capacity"
-            stop.set()
-        except BaseException as e:  # noqa: BLE001
-            errors.append(e)
-            stop.set()
-    thread.join()
-    if errors:
-        raise errors[0]
+            load.join()
+        except BaseException:  # noqa: BLE001 - a failed load matters only if counting got that far
+            if outcome == "counted":
+                raise
     return outcome
 
 

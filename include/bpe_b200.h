@@ -73,6 +73,15 @@ int bpe_set_special_tokens(bpe_ctx* ctx, const uint8_t* h_blob, const uint32_t* 
  * Thread count: BPE_B200_IO_THREADS, default min(16, cores / LOCAL_WORLD_SIZE). */
 int bpe_load_file(bpe_ctx* ctx, const char* path, uint64_t offset, uint64_t n, uint8_t* d_dst, void* stream);
 
+/* The same for n_ranges byte ranges of the file at once: range r = file bytes [file_off[r], file_off[r] + len[r]) goes to
+ * d_base + dev_off[r].  The reference's workers each read their own byte range (pretokenization.py:96-109, :192-194);
+ * here the ranges are the pieces of a large corpus, cut at special-token starts, that the GPU scans and counts while later
+ * pieces are still on their way.  *h_ranges_done (host memory, may be NULL) is updated while the call runs: the number of
+ * leading ranges that are completely in device memory.  The caller polls it from another thread and may use range r as
+ * soon as the value exceeds r.  Same concurrency rule as bpe_load_file (and not beside a bpe_load_file). */
+int bpe_load_file_ranges(bpe_ctx* ctx, const char* path, uint32_t n_ranges, const uint64_t* file_off, const uint64_t* len,
+                         const uint64_t* dev_off, uint8_t* d_base, volatile uint64_t* h_ranges_done, void* stream);
+
 /* Copies n bytes from device memory to an ordinary (pageable) host array through staging buffers of its own, e.g. the
  * ids of bpe_encode into a NumPy array — the 1-D token dataset format.  Waits for `stream` first. */
 int bpe_store_to_host(bpe_ctx* ctx, const void* d_src, uint64_t n, void* h_dst, void* stream);
