@@ -224,6 +224,20 @@ def test_train_matches_port_on_fresh_corpus(style, seed, size, vocab_size, tmp_p
     assert (vocab, merges) == (want_vocab, want_merges)
 
 
+@pytest.mark.parametrize("style,seed,size,vocab_size", [(1, 33, 16_000_000, 2500), (0, 34, 32_000_000, 6000)])
+def test_train_matches_c_oracle_on_larger_corpora(style, seed, size, vocab_size, tmp_path):
+    """OpenWebText-shaped (2*10^5 distinct pretokens, many light steps with deferred updates) and TinyStories-shaped
+    corpora, thousands of merges: ordered merges and vocab equal the C oracle's."""
+    from adapters import run_train_bpe
+
+    path = synth_corpus(style, seed, size, str(tmp_path / "c.txt"))
+    want_vocab, want_merges = c_oracle.train(c_oracle.count(open(path, "rb").read(), [EOT]), vocab_size, [EOT])
+    vocab, merges = run_train_bpe(path, vocab_size, [EOT])
+    bad = next((i for i, (x, y) in enumerate(zip(merges, want_merges)) if x != y), None)
+    assert bad is None, f"merge {bad}: gpu {merges[bad]} oracle {want_merges[bad]}"
+    assert (vocab, merges) == (want_vocab, want_merges)
+
+
 def test_train_ignores_invalid_utf8_like_the_reference(tmp_file):
     """pretokenization.py:194 decodes with errors="ignore"."""
     from adapters import run_train_bpe
@@ -355,6 +369,31 @@ def test_encode_dense_windows_and_warm_cache(gpt2_model):
         assert tok.encode(text) == ct.encode(text)
     long_ids = "z" * 3000 + " " + "ab" * 2000  # two pretokens with hundreds of ids each
     assert tok.encode(long_ids) == ct.encode(long_ids)
+
+
+def test_encode_with_ids_beyond_16_bits(gpt2_model, tmp_path):
+    """A vocabulary whose ids do not fit uint16: ids come back as uint32, the same as the oracle's."""
+    from adapters import get_tokenizer
+
+    vocab, merges = gpt2_model
+    shift = 70_000
+    wide = {(k if k < 256 else k + shift): v for k, v in vocab.items()}
+    wide[max(wide) + 1] = EOT.encode()
+    tok = get_tokenizer(wide, merges, [EOT])
+    ct = c_oracle.COracleTokenizer(wide, merges, [EOT])
+    path = synth_corpus(0, 81, 1_000_000, str(tmp_path / "c.txt"))
+    text = open(path, encoding="utf-8").read()
+    want = ct.encode(text)
+    assert max(want) > 0xFFFF
+    assert tok.encode(text) == want
+    got = tok.encode_file_to_array(path)
+    assert got.dtype == np.uint32 and got.tolist() == ct.encode_lines(text)
+    assert tok.decode(want[:5000]) == ct_decode(wide, want[:5000])
+    assert tok.decode_array(got) == open(path, "rb").read()
+
+
+def ct_decode(vocab, ids):
+    return b"".join(vocab[i] for i in ids).decode("utf-8", errors="replace")
 
 
 def test_encode_keyerror_is_raised_every_time(gpt2_model):
