@@ -147,7 +147,10 @@ __device__ __forceinline__ void set_status(uint32_t* status, uint32_t bit) { ato
 __device__ __forceinline__ uint64_t unique_insert(const UniqueTable& t, uint32_t* status, const uint8_t* __restrict__ text,
                                                   uint64_t p, uint32_t len, TokenKey k, uint64_t c) {
     uint64_t slot = (k.key * 0xD6E8FEB86659FD93ull >> 17) & t.cap_mask;
-    for (uint64_t probe = 0; probe <= t.cap_mask; probe++) {
+    // A probe sequence this long means the table is far too full for open addressing: report it instead of walking all slots
+    // (the host enlarges the table and counts again).  Tables of up to 4096 slots may be walked completely.
+    const uint64_t probe_limit = t.cap_mask < 4096 ? t.cap_mask + 1 : 4096;
+    for (uint64_t probe = 0; probe < probe_limit; probe++) {
         uint64_t cur = *reinterpret_cast<volatile uint64_t*>(t.key + slot);
         if (cur == 0) {
             cur = atomicCAS(reinterpret_cast<unsigned long long*>(t.key + slot), 0ull, (unsigned long long)k.key);
@@ -163,7 +166,9 @@ __device__ __forceinline__ uint64_t unique_insert(const UniqueTable& t, uint32_t
                 t.enc_len[slot] = 0xFFFFFFFFu;
                 __threadfence();
                 *reinterpret_cast<volatile uint32_t*>(t.chk + slot) = k.chk;
-                atomicAdd(reinterpret_cast<unsigned long long*>(t.counters + 1), 1ull);
+                const unsigned long long n_before = atomicAdd(reinterpret_cast<unsigned long long*>(t.counters + 1), 1ull);
+                // beyond 7/8 full (large tables only) the probe sequences explode: stop early, the host enlarges the table
+                if (t.cap_mask >= 4096 && n_before > (t.cap_mask + 1) / 8 * 7) set_status(status, ST_TABLE_FULL);
                 if (c) atomicAdd(reinterpret_cast<unsigned long long*>(t.cnt + slot), (unsigned long long)c);
                 return slot;
             }

@@ -75,6 +75,9 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
     uint64_t local_tokens = 0;
 
     for (uint64_t w0 = w_lo + warp * 32; w0 < w_hi; w0 += COUNT_THREADS) {  // COUNT_THREADS = 32 words x warps per CTA
+        // the call is lost once the table or a pool is full (the host enlarges them and counts again): do not grind on
+        // (one decision per warp: lanes that saw different values would leave the shuffles below a lane short)
+        if (__any_sync(0xFFFFFFFFu, (*reinterpret_cast<volatile uint32_t*>(P.status) & (ST_TABLE_FULL | ST_POOL_FULL)) != 0)) break;
         const uint64_t wi = w0 + lane;
         const uint32_t w = wi < w_hi ? __ldg(P.start + wi) : 0u;
         // exclusive scan of the per-lane token counts
@@ -139,6 +142,7 @@ __global__ void __launch_bounds__(COUNT_THREADS) count_kernel(const CountParams 
     // fold the CTA's table into the context's table
     for (uint32_t s = threadIdx.x; s < COUNT_SLOTS; s += COUNT_THREADS) {
         if (st.key[s] == 0) continue;
+        if (*reinterpret_cast<volatile uint32_t*>(P.status) & (ST_TABLE_FULL | ST_POOL_FULL)) break;  // the call is lost anyway
         uint64_t p = base + st.pos[s];
         uint32_t len = (uint32_t)(token_end(P.start, P.n_words, p >> 5, __ldg(P.start + (p >> 5)), (uint32_t)(p & 31), P.n) - p);
         TokenKey k = hash_bytes(P.text, p, len);  // key again, plus the check word (not kept in shared memory)

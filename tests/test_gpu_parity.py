@@ -448,6 +448,44 @@ def test_pipelined_file_paths_match_whole_file_paths(tmp_path, ts10k_model, monk
     assert got == pt.parallel_pretokenization(str(bad), special_tokens=[EOT])
 
 
+def test_tables_grow_when_a_corpus_outgrows_them(engine, tmp_path, gpt2_model, monkeypatch):
+    """A context configured far too small for the corpus: counting, training and encoding notice (capacity error
+    from the kernels, quickly — not after walking a full table), enlarge the tables and give the usual results."""
+    import time
+
+    from adapters import get_tokenizer, run_train_bpe
+    from bpe_transformer_b200.tokenization.preprocessing import pretokenization as pt
+
+    path = synth_corpus(1, 91, 6_000_000, str(tmp_path / "c.txt"))
+    data = open(path, "rb").read()
+    want = c_oracle.count(data, [EOT])
+    assert len(want) > 50_000
+    before = (engine.table_log2, engine.pool_bytes)
+    try:
+        engine.configure(13, 1 << 16)  # 8192 slots, 64 KiB of pretoken bytes
+        t0 = time.perf_counter()
+        got = pt.parallel_pretokenization(path, special_tokens=[EOT])
+        assert time.perf_counter() - t0 < 20
+        assert got == Counter({tuple(k): v for k, v in want.items()})
+        assert engine.table_log2 > 13
+        engine.configure(13, 1 << 16)
+        monkeypatch.setattr(pt, "_PIPE_BYTES", 1 << 20)  # the piece-by-piece path of large files grows the same way
+        assert pt.parallel_pretokenization(path, special_tokens=[EOT]) == got
+        assert engine.table_log2 > 13
+        monkeypatch.setattr(pt, "_PIPE_BYTES", 1 << 40)
+        engine.configure(13, 1 << 16)
+        vocab, merges = run_train_bpe(path, 600, [EOT])
+        assert (vocab, merges) == c_oracle.train(want, 600, [EOT])
+        engine.configure(13, 1 << 16)
+        gv, gm = gpt2_model
+        gv = with_specials(gv, [EOT])
+        tok = get_tokenizer(gv, gm, [EOT])
+        text = data[:2_000_000].decode("utf-8", errors="ignore")
+        assert tok.encode(text) == c_oracle.COracleTokenizer(gv, gm, [EOT]).encode(text)
+    finally:
+        engine.configure(*before)
+
+
 def test_model_and_dataset_formats(tmp_path, gpt2_model, input_bytes, tmp_file):
     """GPT-2 text formats round trip; a tokenized file lands in a .npy that holds encode_iterable's ids."""
     from adapters import get_tokenizer
