@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(1024) scan_totals_kernel(const uint32_t* __res
 // HBM traffic: N bytes of text + N/8 of mask read, 2T (or 4T) bytes of ids written; the tables sit in L2.
 #define EMIT_THREADS 256
 #define EMIT_WARPS (EMIT_THREADS / 32)
-#define EMIT_KEEP 512        // tokens of a window whose table entries are kept in shared memory between the two passes
+#define EMIT_KEEP 288        // tokens of a window whose table entries are kept in shared memory between the two passes
 #define ST_AGG (1ull << 62)  // state word: window's own count is available
 #define ST_INC (2ull << 62)  // state word: count of this and all earlier windows is available
 
@@ -209,7 +209,7 @@ struct EmitLookup {
 __device__ __forceinline__ uint32_t ent_ids(uint2 e) { return (e.y >> 31) ? ((e.y >> 16) & 0x3FFFu) : e.y; }
 
 template <typename OutT>
-__global__ void __launch_bounds__(EMIT_THREADS, 4) emit_fused_kernel(const EmitParams P, const __grid_constant__ Specials sp, uint64_t n_windows,
+__global__ void __launch_bounds__(EMIT_THREADS, 6) emit_fused_kernel(const EmitParams P, const __grid_constant__ Specials sp, uint64_t n_windows,
                                                                      unsigned long long* __restrict__ state, unsigned long long* __restrict__ ticket,
                                                                      OutT* __restrict__ out, uint64_t cap, unsigned long long* __restrict__ total_out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -267,7 +267,10 @@ __global__ void __launch_bounds__(EMIT_THREADS, 4) emit_fused_kernel(const EmitP
                 const uint32_t inc = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 2), none = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 0);
                 const uint32_t first_inc = inc ? (uint32_t)__ffs(inc) - 1 : 32;  // nearest window whose inclusive prefix is known
                 const uint32_t need = first_inc >= 31 ? 0xFFFFFFFFu : ((2u << first_inc) - 1u);
-                if (none & need) continue;  // a window we depend on has not published yet: look again
+                if (none & need) {  // a window we depend on has not published yet: look again, a little later (every
+                    __nanosleep(128);  // look is 32 loads through L2, and the warps that still have to publish need it)
+                    continue;
+                }
                 unsigned long long part = (lane <= first_inc) ? (v & ~(3ull << 62)) : 0ull;
                 for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
                 before += part;
@@ -429,7 +432,7 @@ int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* 
         CUDA_TRY(ctx, cudaMemsetAsync(buf, 0, (n_windows + 4) * 8, s));
         {
             KernelTimer t(ctx, "emit_fused_kernel", s);
-            const uint64_t blocks = std::min<uint64_t>((n_windows + EMIT_WARPS - 1) / EMIT_WARPS, (uint64_t)BPE_N_SM * 4);
+            const uint64_t blocks = std::min<uint64_t>((n_windows + EMIT_WARPS - 1) / EMIT_WARPS, (uint64_t)BPE_N_SM * 6);
             const size_t smem = EMIT_WARPS * sizeof(EmitWarp);
             if (out_elem_bytes == 2) emit_fused_kernel<uint16_t><<<(unsigned)blocks, EMIT_THREADS, smem, s>>>(P, ctx->sp, n_windows, state, ticket, (uint16_t*)d_out, cap, total_out);
             else emit_fused_kernel<uint32_t><<<(unsigned)blocks, EMIT_THREADS, smem, s>>>(P, ctx->sp, n_windows, state, ticket, (uint32_t*)d_out, cap, total_out);
