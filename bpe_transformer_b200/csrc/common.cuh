@@ -277,6 +277,7 @@ struct bpe_ctx {
     uint64_t idpool_cap = 0;
     uint64_t enc_done = 0;             // number of distinct pretokens already encoded
     bool enc_warm = false;             // the last bpe_encode found every pretoken in the table: try without counting first
+    bool count_attr_set = false, emit_attr_set = false;  // dynamic shared memory limits raised for this device's kernels
     // scratch reused across calls
     void* scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};

@@ -191,10 +191,9 @@ int launch_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t
     per = (per + COUNT_THREADS - 1) / COUNT_THREADS * COUNT_THREADS;
     grid = (P.n_words + per - 1) / per;
     P.words_per_block = per;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!ctx->count_attr_set) {  // per context = per device: function attributes do not carry over to another GPU
         CUDA_TRY(ctx, cudaFuncSetAttribute(count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)COUNT_SMEM));
-        attr_set = true;
+        ctx->count_attr_set = true;
     }
     KernelTimer t(ctx, "count_kernel", s);
     count_kernel<<<(unsigned)grid, COUNT_THREADS, COUNT_SMEM, s>>>(P, ctx->sp);

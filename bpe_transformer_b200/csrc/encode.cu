@@ -412,11 +412,10 @@ int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* 
     unsigned long long* buf = (unsigned long long*)ctx_scratch(ctx, 3, (n_windows + 4) * 8);
     if (!buf) return BPE_ERR_CUDA;
     unsigned long long* ticket = buf, *total_out = buf + 1, *state = buf + 2;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!ctx->emit_attr_set) {  // per context = per device
         CUDA_TRY(ctx, cudaFuncSetAttribute(emit_fused_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(EMIT_WARPS * sizeof(EmitWarp))));
         CUDA_TRY(ctx, cudaFuncSetAttribute(emit_fused_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(EMIT_WARPS * sizeof(EmitWarp))));
-        attr_set = true;
+        ctx->emit_attr_set = true;
     }
     // With a warm table (every pretoken of earlier texts is cached with its ids) the text goes straight to the emit pass;
     // if it meets a pretoken it does not know, the text is counted, the new pretokens are encoded, and the emit runs again.

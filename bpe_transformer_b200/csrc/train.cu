@@ -10,15 +10,19 @@
 //             pair -> pretokens inverted index, :186-199, :291-301, keyed by token; entries go stale and are
 //             re-checked on visit like :260-262).
 //
-// The loop is strictly sequential (~10^4 dependent steps) and each step touches little data, so it is LATENCY bound.
-// One persistent kernel runs it, launched as ONE thread-block cluster (16 CTAs):
-//   * CTA 0 drives.  A "light" step (posting list of <= 2048 words: ~85 % of the steps) is done by CTA 0 alone and
-//     synchronises with __syncthreads only: argmax over the hot list -> filter the posting list (one thread per
-//     word, 16-byte loads) -> rewrite the matching words (one WARP per word) -> bookkeeping.
+// The loop is strictly sequential (~10^4 dependent steps) and each step touches little data, so it is LATENCY bound: what
+// counts is the number of dependent round trips to L2 (~0.8 us each) per step.  One persistent kernel runs it, launched
+// as a cooperative grid with one CTA per SM (BPE_B200_TRAIN_MODE=cluster: one 16-CTA cluster instead):
+//   * CTA 0 drives.  Pairs with a count >= T live in its shared memory (HotCache), so the argmax never leaves the SM.
+//     A "light" step (posting list of <= 2048 words: ~88 % of the steps) is done by CTA 0 alone with __syncthreads only:
+//     argmax -> filter the posting list (four postings in flight per thread) -> rewrite the hits (one WARP per word).
+//     Its count updates do not wait for global memory either: additions go to a per-step shared table (NewPairs),
+//     everything that must reach the global table is queued (Deferred) and applied behind the next step's loads.
 //   * A "heavy" step (a pair of bytes, whose candidates are ALL words, or a long posting list) is broadcast to the
-//     other CTAs, which sleep on the hardware cluster barrier in between.
-// For word tables beyond ~4*10^6 words the same code runs as a cooperative grid (grid barrier instead of the
-// cluster barrier).  No host round trip inside the loop.
+//     other CTAs, which poll a flag in global memory in between (cluster mode: the hardware cluster barrier).
+//     (Four candidates per thread in the heavy filter too was tried: -7 % on a corpus with 6*10^6 words, +4 % on the
+//     2 GB TinyStories-shaped one through register pressure in this shared kernel; not kept.)
+// No host round trip inside the loop; a pinned-host heartbeat and a device watchdog turn a bug into an error, not a hang.
 //
 // The count deltas reproduce the reference exactly, including its double counting:
 // removed neighbours are read from the ORIGINAL word (:414-417), added neighbours are counted once per new
