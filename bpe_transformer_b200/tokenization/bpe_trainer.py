@@ -71,10 +71,11 @@ class BPETrainer:
             if e.code == _lib.ERR_NO_PAIRS:  # :237-240
                 raise AttributeError("Warning: self._vocab_pairs_heap was not initialized. No pairs to start merging process.") from e
             raise
-        for k, (a, b) in enumerate(zip(m_a.tolist(), m_b.tolist())):
-            left, right = self._vocab[a], self._vocab[b]
-            self._merges.append((left, right))  # :310
-            self.add_new_vocab(id=first_new + k, new_value=left + right)  # :314-316
+        vocab, merges = self._vocab, self._merges  # locals: this loop is ~10^4 iterations of pure bookkeeping
+        for k, (a, b) in enumerate(zip(m_a.tolist(), m_b.tolist()), start=first_new):
+            left, right = vocab[a], vocab[b]
+            merges.append((left, right))  # :310
+            vocab[k] = left + right       # add_new_vocab, :314-316
         t = engine.train_timing()
         self.last_timing = {"pair_init_ms": t[0], "merge_loop_ms": t[1], "iterations": t[2], "merges": len(m_a)}
 
