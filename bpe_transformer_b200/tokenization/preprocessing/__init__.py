@@ -1,4 +1,9 @@
-"""Reference: bpe_transformer/tokenization/preprocessing/__init__.py:1-3."""
-from .pretokenization import parallel_pretokenization, pretokenize, serial_pretokenization
+"""Pretokenisation entry points under the names the reference exports (its preprocessing/__init__.py): the three
+file-level functions.  The helpers (chunk offsets, host split, GPU counting) live in `.pretokenization`."""
+from . import pretokenization as _impl
 
-__all__ = ["parallel_pretokenization", "serial_pretokenization", "pretokenize"]
+pretokenize = _impl.pretokenize
+parallel_pretokenization = _impl.parallel_pretokenization
+serial_pretokenization = _impl.serial_pretokenization
+
+__all__ = ["pretokenize", "parallel_pretokenization", "serial_pretokenization"]
