@@ -263,22 +263,9 @@ class BPETokenizer(Tokenizer):
         offs = _cuts_after_newlines(path, lo, hi, _PIPE_BYTES)
         wide = self._bind(engine)
         out = _lib.host_array(hi - lo, np.uint32 if wide else np.uint16)  # one id per byte at most; unused pages stay untouched
-        loaded: queue.Queue = queue.Queue(maxsize=2)
         to_store: queue.Queue = queue.Queue(maxsize=2)
         errors: list[BaseException] = []
         stop = threading.Event()
-
-        def loader():
-            try:
-                torch.cuda.set_device(engine.device)
-                for a, b in zip(offs[:-1], offs[1:]):
-                    if stop.is_set():
-                        break
-                    loaded.put(engine.load_file(path, a, b))
-            except BaseException as e:  # noqa: BLE001 - re-raised on the calling thread
-                errors.append(e)
-            finally:
-                loaded.put(None)
 
         def storer():
             failed = False
@@ -292,37 +279,37 @@ class BPETokenizer(Tokenizer):
                 try:
                     ids, at = item
                     engine.store_into(ids, out[at:at + int(ids.numel())])
-                except BaseException as e:  # noqa: BLE001
+                except BaseException as e:  # noqa: BLE001 - re-raised on the calling thread
                     errors.append(e)
                     failed = True
                     stop.set()
 
-        threads = [threading.Thread(target=loader, daemon=True), threading.Thread(target=storer, daemon=True)]
-        for t in threads:
-            t.start()
+        store_thread = threading.Thread(target=storer, daemon=True)
+        store_thread.start()
+        load = engine.load_file_ranges(path, offs)  # one pass of the I/O lanes over the whole range, on its own thread
         total, has_cr = 0, False
-        while True:
-            item = loaded.get()
-            if item is None:
-                break
-            if stop.is_set():
-                continue  # drain what the loader had in flight
-            d_text, n = item
-            try:
-                if n and bool((d_text[:n] == 13).any().item()):
-                    has_cr = True
-                    stop.set()
+        try:
+            for k in range(len(offs) - 1):
+                if stop.is_set():
+                    break
+                d_text, n = load.piece(k)  # blocks until piece k has landed; later pieces keep arriving meanwhile
+                if not n:
                     continue
+                if bool((d_text[:n] == 13).any().item()):
+                    has_cr = True
+                    break
                 ids = self.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=engine, on_device=(d_text, n))
+                to_store.put((ids, total))
+                total += int(ids.numel())
+        except BaseException as e:  # noqa: BLE001
+            errors.insert(0, e)
+        finally:
+            to_store.put(None)
+            store_thread.join()
+            try:
+                load.join()
             except BaseException as e:  # noqa: BLE001
                 errors.append(e)
-                stop.set()
-                continue
-            to_store.put((ids, total))
-            total += int(ids.numel())
-        to_store.put(None)
-        for t in threads:
-            t.join()
         if errors:
             raise errors[0]
         return None if has_cr else out[:total]
