@@ -389,6 +389,16 @@ class RangeLoad:
         self._check()
 
 
+def pinned_array(n_items: int, dtype) -> np.ndarray:
+    """Page-locked NumPy array (a view of a pinned torch tensor, which it keeps alive): as the `out=` of
+    BPETokenizer.encode_file_to_array it receives the ids by DMA, with no host copy.  Allocate once, reuse across calls —
+    page-locking costs far more than one copy."""
+    import torch
+
+    nbytes = int(n_items) * np.dtype(dtype).itemsize
+    return torch.empty(nbytes, dtype=torch.uint8, pin_memory=True).numpy().view(dtype)
+
+
 def host_array(n_items: int, dtype) -> np.ndarray:
     """Uninitialised NumPy array for results copied back from the GPU.  (Transparent huge pages were tried for the large
     ones and made the first touch by 16 copy threads five times slower on the test box: plain pages it is.)"""

@@ -269,6 +269,16 @@ extern "C" int bpe_store_to_host(bpe_ctx* ctx, const void* d_src, uint64_t n, vo
     CUDA_TRY(ctx, cudaStreamSynchronize((cudaStream_t)stream));  // the producer of d_src has finished
     const uint8_t* src = static_cast<const uint8_t*>(d_src);
     uint8_t* dst = static_cast<uint8_t*>(h_dst);
+    {   // a page-locked destination (cudaHostAlloc / cudaHostRegister, e.g. a pinned torch tensor) takes the DMA directly:
+        // no staging buffer, no host memcpy, no first-touch page faults
+        cudaPointerAttributes attr;
+        if (cudaPointerGetAttributes(&attr, h_dst) == cudaSuccess && attr.type == cudaMemoryTypeHost) {
+            CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, st->copy[0]));
+            CUDA_TRY(ctx, cudaStreamSynchronize(st->copy[0]));
+            return BPE_OK;
+        }
+        cudaGetLastError();  // an ordinary pointer may be reported as an error by older drivers: not ours to keep
+    }
     const uint64_t n_chunks = (n + kLaneBytes - 1) / kLaneBytes;
     std::atomic<uint64_t> next{0};
     int rc = st->run(n_chunks, [&](int lane) -> int {

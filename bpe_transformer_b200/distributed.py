@@ -136,10 +136,10 @@ def train_bpe_sharded(input_path, vocab_size: int, special_tokens: list[str], gr
     return trainer.vocab, trainer.merges
 
 
-def encode_file_sharded(tokenizer, path, group=None) -> tuple[np.ndarray, int, int]:
+def encode_file_sharded(tokenizer, path, group=None, out: np.ndarray | None = None) -> tuple[np.ndarray, int, int]:
     """Every rank encodes its share of the file's lines; returns (ids of this rank, offset of its first id in the
     whole file's id sequence, total ids).  Concatenating the ranks' arrays in rank order gives
-    list(tokenizer.encode_iterable(open(path)))."""
+    list(tokenizer.encode_iterable(open(path))).  `out`: see BPETokenizer.encode_file_to_array."""
     import torch
     import torch.distributed as dist
 
@@ -147,7 +147,7 @@ def encode_file_sharded(tokenizer, path, group=None) -> tuple[np.ndarray, int, i
     engine = _lib.get_engine()
     offs = line_shard_offsets(path, world)
     lo, hi = offs[rank], offs[rank + 1]
-    ids = tokenizer.encode_file_to_array(path, engine=engine, lo=lo, hi=hi)
+    ids = tokenizer.encode_file_to_array(path, engine=engine, lo=lo, hi=hi, out=out)
     counts = [torch.zeros(1, dtype=torch.int64, device=f"cuda:{engine.device}") for _ in range(world)]
     dist.all_gather(counts, torch.tensor([len(ids)], dtype=torch.int64, device=f"cuda:{engine.device}"), group=group)
     counts = [int(c.item()) for c in counts]

@@ -238,22 +238,29 @@ class BPETokenizer(Tokenizer):
             yield from self._ids_to_numpy(self.encode_bytes_to_device(tail.encode(ENCODING_STD), flags=_lib.CUT_AFTER_NEWLINE)).tolist()
 
     def encode_file_to_array(self, path, cut_after_newline: bool = True, engine: "_lib.Engine | None" = None,
-                             lo: int = 0, hi: int | None = None) -> np.ndarray:
+                             lo: int = 0, hi: int | None = None, out: np.ndarray | None = None) -> np.ndarray:
         """Array-returning sibling of encode_iterable(open(path)): the UTF-8 file (or its bytes [lo, hi), which must
         start and end at line ends) -> numpy uint16 / uint32 ids (the format a 1-D token dataset uses).  Files
         with '\\r' go through Python's universal-newline translation first, as open(path) would do.
         Large files move in pieces cut after a newline: one host thread reads the next piece into HBM and another
-        copies the previous piece's ids out while the GPU encodes the current one."""
+        copies the previous piece's ids out while the GPU encodes the current one.
+        `out`: a 1-D C-contiguous array of the id dtype (uint16, or uint32 for vocabularies beyond 65535) to write
+        into instead of a new array; the result is `out[:number of ids]`, ValueError if it is too small.  With a
+        page-locked `out` (`_lib.pinned_array`, reused across calls) the ids arrive by DMA without any host copy."""
         engine = engine or _lib.get_engine()
         size = os.path.getsize(path)
         hi = size if hi is None else min(hi, size)
+        if out is not None:
+            want = np.uint32 if self._model()[6] else np.uint16
+            if out.ndim != 1 or out.dtype != want or not out.flags.c_contiguous or not out.flags.writeable:
+                raise ValueError(f"out must be a writable 1-D C-contiguous {np.dtype(want).name} array")
         if cut_after_newline and hi - lo > _PIPE_BYTES + _PIPE_BYTES // 2:
-            ids = self._encode_file_pipelined(path, lo, hi, engine)
+            ids = self._encode_file_pipelined(path, lo, hi, engine, out)
             if ids is not None:
                 return ids
-        return self.encode_device_to_array(engine.load_file(path, lo, hi), engine, cut_after_newline)
+        return self.encode_device_to_array(engine.load_file(path, lo, hi), engine, cut_after_newline, out)
 
-    def _encode_file_pipelined(self, path, lo: int, hi: int, engine: "_lib.Engine"):
+    def _encode_file_pipelined(self, path, lo: int, hi: int, engine: "_lib.Engine", out: np.ndarray | None = None):
         """None if the file holds a '\\r' (the caller then takes the whole-file path with newline translation)."""
         import queue
         import threading
@@ -262,7 +269,8 @@ class BPETokenizer(Tokenizer):
 
         offs = _cuts_after_newlines(path, lo, hi, _PIPE_BYTES)
         wide = self._bind(engine)
-        out = _lib.host_array(hi - lo, np.uint32 if wide else np.uint16)  # one id per byte at most; unused pages stay untouched
+        if out is None:
+            out = _lib.host_array(hi - lo, np.uint32 if wide else np.uint16)  # one id per byte at most; unused pages stay untouched
         to_store: queue.Queue = queue.Queue(maxsize=2)
         errors: list[BaseException] = []
         stop = threading.Event()
@@ -278,6 +286,8 @@ class BPETokenizer(Tokenizer):
                     continue
                 try:
                     ids, at = item
+                    if at + int(ids.numel()) > out.size:
+                        raise ValueError("out is too small for the ids of this file")
                     engine.store_into(ids, out[at:at + int(ids.numel())])
                 except BaseException as e:  # noqa: BLE001 - re-raised on the calling thread
                     errors.append(e)
@@ -314,11 +324,18 @@ class BPETokenizer(Tokenizer):
             raise errors[0]
         return None if has_cr else out[:total]
 
-    def encode_device_to_array(self, on_device, engine: "_lib.Engine", cut_after_newline: bool = True) -> np.ndarray:
+    def encode_device_to_array(self, on_device, engine: "_lib.Engine", cut_after_newline: bool = True,
+                               out: np.ndarray | None = None) -> np.ndarray:
         """(padded device text, length) -> NumPy ids, cutting after every newline like a file handle's line iteration."""
         d_text, n = on_device
         if n and bool((d_text[:n] == 13).any().item()):  # '\r': what text mode translates before the reference sees lines
             data = d_text[:n].cpu().numpy().tobytes().replace(b"\r\n", b"\n").replace(b"\r", b"\n")
             on_device = engine.to_device(data)
         ids = self.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE if cut_after_newline else 0, engine=engine, on_device=on_device)
-        return engine.to_host_array(ids, np.uint16 if ids.element_size() == 2 else np.uint32)
+        if out is None:
+            return engine.to_host_array(ids, np.uint16 if ids.element_size() == 2 else np.uint32)
+        k = int(ids.numel())
+        if k > out.size:
+            raise ValueError("out is too small for the ids of this file")
+        engine.store_into(ids, out[:k])
+        return out[:k]

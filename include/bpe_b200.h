@@ -83,7 +83,8 @@ int bpe_load_file_ranges(bpe_ctx* ctx, const char* path, uint32_t n_ranges, cons
                          const uint64_t* dev_off, uint8_t* d_base, volatile uint64_t* h_ranges_done, void* stream);
 
 /* Copies n bytes from device memory to an ordinary (pageable) host array through staging buffers of its own, e.g. the
- * ids of bpe_encode into a NumPy array — the 1-D token dataset format.  Waits for `stream` first. */
+ * ids of bpe_encode into a NumPy array — the 1-D token dataset format.  Waits for `stream` first.  A destination that
+ * is page-locked already (cudaHostAlloc / cudaHostRegister) receives the DMA directly, without staging. */
 int bpe_store_to_host(bpe_ctx* ctx, const void* d_src, uint64_t n, void* h_dst, void* stream);
 
 /* ---- pretokenisation ---------------------------------------------------------------------------------- */

@@ -429,6 +429,19 @@ def test_pipelined_file_paths_match_whole_file_paths(tmp_path, ts10k_model, monk
     assert run_train_bpe(path, 1500, [EOT]) == whole_model
     ids = tok.encode_file_to_array(path)
     assert ids.dtype == whole_ids.dtype and np.array_equal(ids, whole_ids)
+    # into a caller's array: page-locked (ids arrive by DMA) and ordinary, piece by piece and whole-file
+    from bpe_transformer_b200 import _lib
+    for buf in (_lib.pinned_array(len(whole_ids) + 10, np.uint16), np.zeros(len(whole_ids), dtype=np.uint16)):
+        for pipe in (1 << 20, 1 << 40):
+            monkeypatch.setattr(tk, "_PIPE_BYTES", pipe)
+            buf[:] = 0
+            got = tok.encode_file_to_array(path, out=buf)
+            assert np.shares_memory(got, buf) and np.array_equal(got, whole_ids)
+    monkeypatch.setattr(tk, "_PIPE_BYTES", 1 << 20)
+    with pytest.raises(ValueError):
+        tok.encode_file_to_array(path, out=np.zeros(len(whole_ids) - 1, dtype=np.uint16))
+    with pytest.raises(ValueError):
+        tok.encode_file_to_array(path, out=np.zeros(len(whole_ids), dtype=np.uint32))
     size = os.path.getsize(path)
     cuts = tk._cuts_after_newlines(path, 0, size, size // 3)
     parts = [tok.encode_file_to_array(path, lo=a, hi=b) for a, b in zip(cuts[:-1], cuts[1:])]
