@@ -78,67 +78,145 @@ def cut_sample(path: str, nbytes: int, out: str) -> int:
 # ---------------------------------------------------------------------------------------------------------
 # CPU side: the reference's algorithm (port), all host cores
 # ---------------------------------------------------------------------------------------------------------
+def merges_sha256(merges) -> str:
+    import hashlib
+
+    h = hashlib.sha256()
+    for a, b in merges:
+        h.update(a.hex().encode() + b" " + b.hex().encode() + b"\n")
+    return h.hexdigest()
+
+
+def cpu_train_full(path: str) -> dict:
+    """The reference's algorithm (oracle/bpe_ref_port.py: regex + Counter + Pool + heapq) over the WHOLE corpus, all host
+    cores, timed once.  Returns the measured seconds and the results (Counter of pretokens, vocab, merges) for parity."""
+    import bpe_ref_port as port
+
+    cores = os.cpu_count() or 1
+    total = os.path.getsize(path)
+    t0 = time.perf_counter()
+    words = port.count_pretokens(path, cores, [EOT])
+    t_pre = time.perf_counter() - t0
+    counter = words.copy()  # train_from_counts consumes its argument
+    t0 = time.perf_counter()
+    vocab, merges = port.train_from_counts(words, VOCAB_SIZE, [EOT])
+    t_merge = time.perf_counter() - t0
+    return {"value": t_pre + t_merge, "unit": "s", "cores": cores, "kind": "port",
+            "sample": f"full corpus, 1 measured run: {total} B, pretokenize+count on {cores} processes {t_pre:.2f} s, "
+                      f"pair histogram + merge loop to {len(merges)} merges {t_merge:.2f} s",
+            "pretokenize_s": t_pre, "merge_s": t_merge, "_counter": counter, "_vocab": vocab, "_merges": merges}
+
+
 def cpu_train_sample(path: str, total_bytes: int, sample_bytes: int) -> dict:
+    """Dispersion only (never the reported value): pretokenize+count of a prefix, scaled to the corpus."""
     import bpe_ref_port as port
 
     cores = os.cpu_count() or 1
     sample = path + f".sample{sample_bytes}"
     n_sample = cut_sample(path, sample_bytes, sample)
     t0 = time.perf_counter()
-    words = port.count_pretokens(sample, cores, [EOT])
+    port.count_pretokens(sample, cores, [EOT])
     t_pre = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    _, merges = port.train_from_counts(words, VOCAB_SIZE, [EOT])
-    t_merge = time.perf_counter() - t0
     os.unlink(sample)
-    est = t_pre * total_bytes / n_sample + t_merge
-    return {"value": est, "unit": "s", "cores": cores, "kind": "port",
-            "sample": f"first {n_sample} B of the corpus: pretokenize+count on {cores} processes {t_pre:.2f} s (scaled x{total_bytes / n_sample:.1f}), "
-                      f"merge loop to {len(merges)} merges on the sample's Counter {t_merge:.2f} s (not scaled: a lower bound, the full corpus has more distinct pretokens)",
-            "pretokenize_s_sample": t_pre, "merge_s_sample": t_merge, "sample_bytes": n_sample}
+    return {"pretokenize_s_scaled": t_pre * total_bytes / n_sample, "sample_bytes": n_sample}
 
 
-def cpu_encode_sample(path: str, vocab, merges, sample_bytes: int) -> dict:
+def cpu_encode_sample(path: str, vocab, merges, serial_bytes: int, parallel_bytes: int) -> dict:
+    """BPETokenizer.encode_iterable of the reference (port) over prefixes of the corpus: the serial variant and the
+    n_workers=cpu_count() variant (bpe_tokenizer.py:381-423), the faster one is the baseline.  Returns the serial ids too."""
+    import numpy as np
+
     import bpe_ref_port as port
 
-    sample = path + f".encsample{sample_bytes}"
-    n_sample = cut_sample(path, sample_bytes, sample)
-    tok = port.PortTokenizer(vocab, merges, [EOT])
-    t0 = time.perf_counter()
-    n_ids = 0
-    with open(sample, encoding="utf-8") as fh:
-        for _ in tok.encode_iterable(fh):
-            n_ids += 1
-    dt = time.perf_counter() - t0
-    os.unlink(sample)
-    return {"value": n_sample / dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
-            "sample": f"encode_iterable (serial: the reference's parallel variant is slower, SURVEY.md §6.2) over the first {n_sample} B, {n_ids} ids in {dt:.2f} s"}
+    cores = os.cpu_count() or 1
+    out = {}
+    ids_serial = None
+    for name, nbytes, workers in (("serial", serial_bytes, None), ("parallel", parallel_bytes, cores)):
+        sample = path + f".encsample{nbytes}"
+        n_sample = cut_sample(path, nbytes, sample)
+        tok = port.PortTokenizer(vocab, merges, [EOT])
+        t0 = time.perf_counter()
+        with open(sample, encoding="utf-8") as fh:
+            ids = np.fromiter(tok.encode_iterable(fh, n_workers=workers), dtype=np.uint32)
+        dt = time.perf_counter() - t0
+        os.unlink(sample)
+        out[name] = {"GBps": n_sample / dt / 1e9, "sample_bytes": n_sample, "seconds": dt, "ids": int(ids.size), "n_workers": workers or 1}
+        if name == "serial":
+            ids_serial = ids
+    best = max(("serial", "parallel"), key=lambda k: out[k]["GBps"])
+    return {"value": out[best]["GBps"], "unit": "GB/s", "cores": out[best]["n_workers"], "kind": "port", "variant": best,
+            "sample": f"encode_iterable over a prefix cut at a document end: serial {out['serial']['sample_bytes']} B in {out['serial']['seconds']:.2f} s, "
+                      f"n_workers={cores} {out['parallel']['sample_bytes']} B in {out['parallel']['seconds']:.2f} s; the faster ({best}) is the baseline",
+            "serial": out["serial"], "parallel": out["parallel"], "_ids_serial": ids_serial, "_serial_bytes": out["serial"]["sample_bytes"]}
+
+
+def c_oracle_ids_sha256(path: str, vocab, merges) -> tuple[str, int]:
+    """sha256 of the uint16 ids the C oracle (oracle/bpe_oracle.c: sequential scanner + literal one-merge-at-a-time
+    encoder) gives for encode_iterable(open(path)) over the whole file.  Lines are independent segments there, so the
+    file is cut after newlines into ranges that host threads encode side by side (ctypes releases the GIL)."""
+    import hashlib
+    from concurrent.futures import ThreadPoolExecutor
+
+    import numpy as np
+
+    import c_oracle
+
+    data = np.fromfile(path, dtype=np.uint8)
+    n = int(data.size)
+    cores = os.cpu_count() or 1
+    n_ranges = max(1, min(cores * 4, n // (4 << 20)))
+    cuts = [0]
+    for k in range(1, n_ranges):
+        at = max(cuts[-1], k * n // n_ranges)
+        nl = np.flatnonzero(data[at:at + (1 << 20)] == 10)
+        cuts.append(at + int(nl[0]) + 1 if nl.size else cuts[-1])
+    cuts.append(n)
+    ct = c_oracle.COracleTokenizer(vocab, merges, [EOT])
+
+    def work(k):
+        lo, hi = cuts[k], cuts[k + 1]
+        if hi <= lo:
+            return np.empty(0, dtype=np.uint16)
+        return ct.encode_array(data[lo:hi], flags=c_oracle.CUT_AFTER_NEWLINE).astype(np.uint16)
+
+    h = hashlib.sha256()
+    total = 0
+    with ThreadPoolExecutor(max_workers=cores) as pool:
+        for part in pool.map(work, range(len(cuts) - 1)):
+            h.update(part.tobytes())
+            total += int(part.size)
+    return h.hexdigest(), total
 
 
 def run_reference(args, rank: int, world: int) -> None:
     """--impl reference: the reference's own CPU implementation of the path (the port: the reference is pure
-    Python and /root/reference does not travel), all host cores, same metric / unit / config."""
+    Python and /root/reference does not travel), all host cores, same metric / unit / config.  The value is ONE
+    measured run over the whole corpus (~1 min on 16-32 cores), whatever --steps says: repeating it K times would take
+    the run far beyond "a few minutes".  Further steps time the pretokenisation of a 64 MB prefix, for dispersion only."""
     if rank != 0:
         return
     path = corpus_path(args.bytes)
     make_corpus(path, args.bytes)
     total = os.path.getsize(path)
-    sample_bytes = min(total, args.cpu_sample_bytes)
-    runs = []
-    for i in range(args.warmup + args.steps):
-        r = cpu_train_sample(path, total, sample_bytes)
-        if i >= args.warmup:
-            runs.append(r)
-        log(f"[reference] step {i}: {r['value']:.1f} s estimated ({r['pretokenize_s_sample']:.2f} + {r['merge_s_sample']:.2f} s on the sample)")
-    value = sum(r["value"] for r in runs) / len(runs)
-    base = runs[-1]
+    full = cpu_train_full(path)
+    log(f"[reference] full corpus: {full['value']:.1f} s ({full['pretokenize_s']:.1f} + {full['merge_s']:.1f})")
+    extra = []
+    for _ in range(min(2, max(0, args.steps - 1))):
+        extra.append(cpu_train_sample(path, total, min(total, args.cpu_sample_bytes)))
+    value = full["value"]
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": value * 1e3, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": workload_config(total, world),
-        "cpu_baseline": {"value": value, "unit": "s", "cores": base["cores"], "kind": "port", "sample": base["sample"]},
+        "cpu_baseline": {"value": value, "unit": "s", "cores": full["cores"], "kind": "port", "sample": full["sample"]},
         "e2e": {"value": value, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "timed_runs": 1, "merges": len(full["_merges"]), "merges_sha256": merges_sha256(full["_merges"]),
+        "dispersion_pretokenize_64MB_scaled_s": [round(e["pretokenize_s_scaled"], 2) for e in extra],
     }
+    if not args.no_cpu_encode:
+        enc = cpu_encode_sample(path, full["_vocab"], full["_merges"], min(total, 16_000_000), min(total, 2_000_000))
+        line["encode"] = {"metric": "encode_GBps_corpus_to_uint16", "value": enc["value"], "unit": "GB/s", "variant": enc["variant"], "cores": enc["cores"],
+                          "sample": enc["sample"]}
     print(json.dumps(line), flush=True)
 
 

@@ -48,7 +48,8 @@ int ctx_status_to_code(bpe_ctx* ctx, uint32_t st) {
     if (st & ST_POOL_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "pretoken byte / id pool full (bpe_ctx_configure: pool_bytes)");
     if (st & ST_PAIR_TABLE_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "pair table full");
     if (st & ST_WATCHDOG) return ctx_fail(ctx, BPE_ERR_CUDA, "merge loop watchdog: no progress for 60 s (internal error)");
-    if (st & ST_LIST_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "posting pool / token byte pool full");
+    if (st & ST_LIST_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "posting pool full");
+    if (st & ST_BLOB_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "token byte pool full");
     return ctx_fail(ctx, BPE_ERR_CUDA, "unknown status bits");
 }
 
@@ -124,6 +125,7 @@ void bpe_ctx_destroy(bpe_ctx* ctx) {
     cudaFree(ctx->d_mkey); cudaFree(ctx->d_mrank); cudaFree(ctx->d_mid); cudaFree(ctx->d_byte_to_id); cudaFree(ctx->d_special_id);
     cudaFree(ctx->d_idpool);
     for (auto& p : ctx->scratch) cudaFree(p);
+    if (ctx->h_beat) cudaFreeHost(ctx->h_beat);
     delete ctx;
 }
 

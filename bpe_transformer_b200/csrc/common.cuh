@@ -21,6 +21,7 @@ enum : uint32_t {
     ST_LIST_FULL = 1u << 6,
     ST_WATCHDOG = 1u << 7,
     ST_ENC_MISS = 1u << 8,  // encode: a pretoken of the text is not in the table yet (handled inside bpe_encode)
+    ST_BLOB_FULL = 1u << 9,  // train: the pool of token byte strings is full (handled inside bpe_train: larger pool, run again)
 };
 
 // ---- code-point classes (include/bpe_unicode_tables.h) --------------------------------------------------
@@ -281,6 +282,7 @@ struct bpe_ctx {
     // scratch reused across calls
     void* scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t* h_beat = nullptr;  // train.cu: pinned host words the merge loop writes its progress to
     void* io_staging[2] = {nullptr, nullptr};  // io.cu: pinned staging buffers + copy streams; [0] loads, [1] stores (they may overlap)
     // timing
     bool profiling = false;

@@ -62,8 +62,8 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_new_kernel(UniqueTable ut,
     if (base + len > idpool_cap) { if (lane == 0) set_status(status, ST_POOL_FULL); return; }
     uint32_t* ids = idpool + base;
     // A pretoken that cannot be encoded (a byte or a merged pair without an id: KeyError at bpe_tokenizer.py:206 / :290)
-    // is left unpublished and nothing is raised here: the table may hold pretokens of earlier texts.  The emit pass raises
-    // when the text being encoded really contains it, on every call.
+    // gets a tombstone entry and nothing is raised here: the table may hold pretokens of earlier texts.  The emit pass
+    // raises when the text being encoded really contains it, on every call.
     bool bad = false;
     for (uint32_t i = lane; i < len; i += 32) {
         uint32_t id = __ldg(byte_to_id + src[i]);
@@ -103,6 +103,13 @@ __global__ void __launch_bounds__(ENC_THREADS) encode_new_kernel(UniqueTable ut,
         }
         cur--;
         __syncwarp();
+    }
+    if (lane == 0 && bad) {
+        // Tombstone: the key is in the table (probe chains stay whole, the slot is not listed again), the value says
+        // "no ids": the emit pass raises ST_MISSING_ID whenever the text being encoded contains this pretoken.
+        const uint64_t key = ut.key[slot];
+        ut.enc_len[slot] = 0xFFFFFFFEu;
+        ut.enc[slot] = make_uint4((uint32_t)key, (uint32_t)(key >> 32), 0u, 0xFFFFFFFFu);
     }
     if (lane == 0 && !bad) {
         ut.enc_off[slot] = (uint32_t)base;
@@ -196,7 +203,13 @@ struct EmitLookup {
             uint64_t slot = (key * 0xD6E8FEB86659FD93ull >> 17) & P.ut.cap_mask;  // the slot sequence of unique_find
             for (uint64_t probe = 0; probe <= P.ut.cap_mask; probe++) {
                 const uint4 e = __ldg(P.ut.enc + slot);
-                if (e.x == (uint32_t)key && e.y == (uint32_t)(key >> 32)) return make_uint2(e.z, e.w);
+                if (e.x == (uint32_t)key && e.y == (uint32_t)(key >> 32)) {
+                    if (e.w == 0xFFFFFFFFu) {  // tombstone of a pretoken that has no encoding (KeyError at bpe_tokenizer.py:206 / :290)
+                        set_status(P.status, ST_MISSING_ID);
+                        return make_uint2(0u, 0u);
+                    }
+                    return make_uint2(e.z, e.w);
+                }
                 if ((e.x | e.y) == 0) break;
                 slot = (slot + 1) & P.ut.cap_mask;
             }

@@ -593,6 +593,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
     __shared__ Command sh_cmd;
     __shared__ bool sh_stop;
     __shared__ unsigned long long sh_px;  // prefix key of the step's new token
+    __shared__ bool sh_blob_full;         // the token byte pool is full: leave the loop, the host enlarges it and trains again
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_words = S.ctrl->n_words;
 
@@ -638,7 +639,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
 #pragma unroll
     for (int r = 0; r < PEND; r++) { pend_e[r] = -1; pend_v[r] = 0; }
     for (uint32_t k = tid; k < NPS; k += NT) { NP.key[k] = 0; NP.cnt[k] = 0; }
-    if (tid == 0) { NP.overflow = 0; DQ.n = 0; }
+    if (tid == 0) { NP.overflow = 0; DQ.n = 0; sh_blob_full = false; }
     __syncthreads();
     while (next_id < S.vocab_size) {
         if ((++passes & 255u) == 0) {  // watchdog: a bug must not hang the GPU (default 120 s, far beyond any real training)
@@ -880,7 +881,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
                         else if (i < 8) px_lo = v << (56 - 8 * i);
                     }
                 }
-            } else if (lane == 0) set_status(S.status, ST_LIST_FULL);
+            } else if (lane == 0) { set_status(S.status, ST_BLOB_FULL); sh_blob_full = true; }
             px_hi = __reduce_or_sync(0xFFFFFFFFu, px_hi);
             px_lo = __reduce_or_sync(0xFFFFFFFFu, px_lo);
             if (lane == 0) {
@@ -1050,6 +1051,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
             next_id++;
         }
         __syncthreads();  // cache and leader stores are ordered before the next argmax of this CTA
+        if (sh_blob_full) break;  // written by the bookkeeping warp before the barrier: every thread sees the same value
         if (tracer) {
             long long c5 = clock64();
             if (list_tok != NONE && list_len <= LIGHT_MAX) {
@@ -1084,8 +1086,27 @@ size_t next_pow2(size_t v) { size_t p = 1; while (p < v) p <<= 1; return p; }
 
 }  // namespace
 
+static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const uint8_t* h_init_blob, const uint32_t* h_init_off,
+                          uint32_t* h_merge_a, uint32_t* h_merge_b, uint32_t* n_merges, uint64_t blob_per_token, bool* blob_full, cudaStream_t s);
+
+// The pool of token byte strings starts at 256 bytes per vocabulary entry; a corpus whose tokens grow longer than that
+// (long runs of one character double a token's length with every merge) fills it, the loop stops, and the training
+// runs again — it is deterministic and rebuilds its words from the context's table — with a pool 16 times larger.
 int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const uint8_t* h_init_blob, const uint32_t* h_init_off,
               uint32_t* h_merge_a, uint32_t* h_merge_b, uint32_t* n_merges, cudaStream_t s) {
+    uint64_t per_token = 256;
+    if (const char* f = getenv("BPE_B200_TRAIN_BLOB_PER_TOKEN")) per_token = (uint64_t)std::max(1, atoi(f));  // tests: force the retry
+    for (;;) {
+        bool blob_full = false;
+        const int rc = run_train_once(ctx, vocab_size, first_new_id, h_init_blob, h_init_off, h_merge_a, h_merge_b, n_merges, per_token, &blob_full, s);
+        if (!blob_full) return rc;
+        if ((uint64_t)h_init_off[first_new_id] + (uint64_t)vocab_size * per_token * 16 >= 0xFFFFFFF0ull) return ctx_status_to_code(ctx, ST_BLOB_FULL);
+        per_token *= 16;
+    }
+}
+
+static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const uint8_t* h_init_blob, const uint32_t* h_init_off,
+                          uint32_t* h_merge_a, uint32_t* h_merge_b, uint32_t* n_merges, uint64_t blob_per_token, bool* blob_full, cudaStream_t s) {
     *n_merges = 0;
     if (!ctx->ut_alloc) return ctx_fail(ctx, BPE_ERR_NO_PAIRS, "no pretokens counted");
     uint64_t h_counters[4];
@@ -1104,7 +1125,7 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     const size_t ph_cap = next_pow2(std::max<size_t>(1u << 16, 2 * n_sym));
     S.ph_mask = ph_cap - 1;
     const uint32_t init_bytes = h_init_off[first_new_id];
-    S.blob_cap = init_bytes + vocab_size * 256u;
+    S.blob_cap = (uint32_t)std::min<uint64_t>(0xFFFFFFF0ull, init_bytes + (uint64_t)vocab_size * blob_per_token);
     S.wl_cap = (uint32_t)n_sym + 16;
     // one allocation, carved up (all sizes rounded to 256 B)
     struct Part { void** p; size_t bytes; };
@@ -1170,8 +1191,8 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     }
 
     // Progress words in pinned host memory: if the loop ever stalls the host says where instead of hanging silently.
-    static uint32_t* h_beat = nullptr;
-    if (!h_beat) CUDA_TRY(ctx, cudaHostAlloc((void**)&h_beat, 2 * 4096 * sizeof(uint32_t), cudaHostAllocMapped));
+    if (!ctx->h_beat) CUDA_TRY(ctx, cudaHostAlloc((void**)&ctx->h_beat, 2 * 4096 * sizeof(uint32_t), cudaHostAllocMapped));
+    uint32_t* h_beat = ctx->h_beat;  // per context: two engines training from two threads must not share it
     memset(h_beat, 0, 2 * 4096 * sizeof(uint32_t));
     uint32_t* d_beat = nullptr;
     CUDA_TRY(ctx, cudaHostGetDevicePointer((void**)&d_beat, h_beat, 0));
@@ -1275,5 +1296,7 @@ int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
         fprintf(stderr, "[bpe_train] merge loop %.2f ms, %u iterations, %u heavy steps, %u rebuilds, driver CTA on SM %u\n", ms1, h_ctrl.n_iters,
                 h_ctrl.n_heavy, h_ctrl.n_rebuilds, h_ctrl.dbg[7]);
     for (auto& e : ev) cudaEventDestroy(e);
-    return ctx_status_to_code(ctx, ctx_read_status(ctx, s));
+    const uint32_t st = ctx_read_status(ctx, s);
+    if (st == ST_BLOB_FULL) { *blob_full = true; return BPE_OK; }  // nothing else went wrong: the caller retries with a larger pool
+    return ctx_status_to_code(ctx, st);
 }

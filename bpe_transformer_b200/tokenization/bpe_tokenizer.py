@@ -3,6 +3,7 @@ runs in csrc/scan.cu, count.cu and encode.cu through the C-ABI (include/bpe_b200
 from __future__ import annotations
 
 import io
+import itertools
 import os
 import pickle
 from collections.abc import Iterable, Iterator
@@ -19,6 +20,8 @@ _BATCH_BYTES = 64 << 20  # encode_iterable hands the GPU about this much text at
 
 
 _PIPE_BYTES = int(os.environ.get("BPE_B200_PIPE_BYTES", str(128 << 20)))  # piece size of the load / encode / store pipeline
+_FIRST_BATCH_BYTES = 1 << 20  # encode_iterable over arbitrary chunks: first ids after ~1 MB of text, batches double up to _BATCH_BYTES
+_serials = itertools.count(1)  # one number per tokenizer object, never reused (id() is: CPython recycles addresses)
 
 
 def _cuts_after_newlines(path, lo: int, hi: int, piece: int) -> list[int]:
@@ -63,6 +66,7 @@ class BPETokenizer(Tokenizer):
         self._bytes_to_id_cache = None
         self._merges_priority = {merge: i for i, merge in enumerate(merges)}  # later duplicate wins (:55)
         self._device_model = None
+        self._serial = next(_serials)  # names this object's model in the engine: a loaded model is reused only for the same object
 
     # -- the reference's accessors ------------------------------------------------------------------------
     @property
@@ -130,7 +134,7 @@ class BPETokenizer(Tokenizer):
     def _bind(self, engine: "_lib.Engine"):
         a, b, m, byte_to_id, special_id, specials, wide = self._model()
         engine.set_special_tokens(specials)
-        engine.load_model((id(self), len(self._merges), len(self._vocab)), a, b, m, byte_to_id, special_id)
+        engine.load_model((self._serial, len(self._merges), len(self._vocab)), a, b, m, byte_to_id, special_id)
         return wide
 
     def encode_bytes_to_device(self, data, cuts=None, flags: int = 0, engine: "_lib.Engine | None" = None, on_device=None):
@@ -197,6 +201,7 @@ class BPETokenizer(Tokenizer):
         cuts: list[int] = []
         total = 0
         pending = ""
+        batch = _FIRST_BATCH_BYTES  # small first batches keep the generator lazy; large ones later keep the GPU busy
         for chunk in iterable:
             pending += chunk
             cut = pending.rfind("\n")
@@ -207,9 +212,10 @@ class BPETokenizer(Tokenizer):
             pieces.append(raw)
             total += len(raw)
             cuts.append(total)
-            if total >= _BATCH_BYTES:
+            if total >= batch:
                 yield from self._ids_to_numpy(self.encode_bytes_to_device(b"".join(pieces), cuts=cuts[:-1])).tolist()
                 pieces, cuts, total = [], [], 0
+                batch = min(batch * 2, _BATCH_BYTES)
         if pending:
             raw = pending.encode(ENCODING_STD)
             pieces.append(raw)
@@ -222,8 +228,10 @@ class BPETokenizer(Tokenizer):
         """A text file handle iterates by lines, so every newline is a cut: read big blocks instead of lines and
         let the kernel cut after each newline (same ids, no per-line Python work)."""
         tail = ""
+        batch = _FIRST_BATCH_BYTES
         while True:
-            block = fh.read(_BATCH_BYTES)
+            block = fh.read(batch)
+            batch = min(batch * 2, _BATCH_BYTES)
             if not block:
                 break
             block = tail + block

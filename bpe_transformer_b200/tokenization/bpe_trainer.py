@@ -52,6 +52,16 @@ class BPETrainer:
             vocab[idx] = token.encode(self.encoding)
         return vocab
 
+    def set_special_token_order(self, order: list[str]) -> None:
+        """Rebuild the initial vocabulary with the special tokens at ids 256.. in the given order (the reference's own
+        order is a set's, i.e. arbitrary per process; ranks that train together must agree on one).  Before training only."""
+        if set(order) != self._special_tokens or self._merges:
+            raise ValueError("set_special_token_order: not the trainer's special tokens, or training has started")
+        vocab = {i: bytes([i]) for i in range(256)}
+        for idx, token in enumerate(order, start=256):
+            vocab[idx] = token.encode(self.encoding)
+        self._vocab = vocab
+
     def add_new_vocab(self, id: int, new_value: bytes) -> None:
         self._vocab[id] = new_value
 

@@ -158,7 +158,12 @@ def _count_file_pipelined(engine: "_lib.Engine", file_path, special_tokens: list
     size = os.path.getsize(file_path)
     with open(file_path, "rb") as fh:
         offs = find_chunk_boundaries(fh, max(2, -(-size // _PIPE_BYTES)), special_tokens)
-    load = engine.load_file_ranges(file_path, offs)  # one pass of the I/O lanes over the whole file, on its own thread
+    return _count_pieces_pipelined(engine, file_path, offs)
+
+
+def _count_pieces_pipelined(engine: "_lib.Engine", file_path, offs: list[int]) -> str:
+    """The byte ranges [offs[k], offs[k+1]) of the file (cut at special-token starts), streamed and counted."""
+    load = engine.load_file_ranges(file_path, offs)  # one pass of the I/O lanes over the whole range, on its own thread
     outcome = "counted"
     try:
         for k in range(len(offs) - 1):

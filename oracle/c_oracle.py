@@ -53,9 +53,15 @@ def _specials(specials):
     return order, blob, off
 
 
-def scan(data: bytes, specials=None, cuts=None, flags: int = 0) -> np.ndarray:
-    """Token-start bitmask (uint32 words, bit i of word i//32 = byte i starts a token)."""
-    t = np.frombuffer(data + b"\0", dtype=np.uint8)
+def scan(data, specials=None, cuts=None, flags: int = 0) -> np.ndarray:
+    """Token-start bitmask (uint32 words, bit i of word i//32 = byte i starts a token).  `data`: bytes, or a
+    contiguous uint8 array (no copy; orc_scan never reads past n)."""
+    if isinstance(data, np.ndarray):
+        t = np.ascontiguousarray(data, dtype=np.uint8)
+        if t.size == 0:
+            t = np.zeros(1, dtype=np.uint8)
+    else:
+        t = np.frombuffer(data + b"\0", dtype=np.uint8)
     n = len(data)
     order, blob, off = _specials(specials)
     cu = np.asarray(cuts if cuts is not None else [], dtype=np.uint64)
@@ -152,16 +158,22 @@ class COracleTokenizer:
         self.n_merges = len(a)
         self.byte_to_id = np.asarray([id_of.get(bytes([k]), 0xFFFFFFFF) for k in range(256)], dtype=np.uint32)
 
-    def encode_bytes(self, data: bytes, cuts=None, flags: int = 0) -> list[int]:
+    def encode_array(self, data, cuts=None, flags: int = 0) -> np.ndarray:
+        """ids (uint32 array) of `data` (bytes or a contiguous uint8 array).  Thread-safe: callers may run several
+        ranges side by side (ctypes releases the GIL around the C calls)."""
         order, blob, off = _specials(self.specials)
         sid = np.asarray([self.id_of[s] for s in order] + [0], dtype=np.uint32)  # KeyError like :175
         start = scan(data, self.specials, cuts, flags)
-        if any(self.byte_to_id[b] == 0xFFFFFFFF for b in set(data)):
+        t = np.ascontiguousarray(data, dtype=np.uint8) if isinstance(data, np.ndarray) else np.frombuffer(data + b"\0", dtype=np.uint8)
+        n = len(data)
+        present = np.flatnonzero(np.bincount(t[:n], minlength=256))
+        if any(self.byte_to_id[b] == 0xFFFFFFFF for b in present):
             raise KeyError("byte missing from vocab")
-        t = np.frombuffer(data + b"\0", dtype=np.uint8)
-        out = np.zeros(len(data) + 1, dtype=np.uint32)
+        if n == 0:
+            return np.zeros(0, dtype=np.uint32)
+        out = np.zeros(n + 1, dtype=np.uint32)
         n_out = C.c_uint64(0)
-        rc = lib().orc_encode(_p(t, C.c_uint8), C.c_uint64(len(data)), _p(start, C.c_uint32), _p(blob, C.c_uint8),
+        rc = lib().orc_encode(_p(t, C.c_uint8), C.c_uint64(n), _p(start, C.c_uint32), _p(blob, C.c_uint8),
                               _p(off, C.c_uint32), len(order), _p(sid, C.c_uint32), _p(self.byte_to_id, C.c_uint32),
                               _p(self.m_a, C.c_uint32), _p(self.m_b, C.c_uint32), _p(self.m_id, C.c_uint32),
                               C.c_uint32(self.n_merges), _p(out, C.c_uint32), C.c_uint64(len(out)), C.byref(n_out))
@@ -169,7 +181,10 @@ class COracleTokenizer:
             raise KeyError("merged bytes missing from vocab")
         if rc:
             raise RuntimeError(f"orc_encode rc={rc}")
-        return out[:n_out.value].tolist()
+        return out[:n_out.value]
+
+    def encode_bytes(self, data: bytes, cuts=None, flags: int = 0) -> list[int]:
+        return self.encode_array(data, cuts, flags).tolist()
 
     def encode(self, text: str) -> list[int]:
         return self.encode_bytes(text.encode("utf-8"))

@@ -11,6 +11,7 @@ What it writes (all gzip'd JSON, byte strings as hex):
   ts10k_model.json.gz  notebooks/sample_data/bpe_tokenizer/{vocab,merges}.pkl (10,000 entries / 9,743 merges)
   course_golden.json.gz  tests/fixtures/train-bpe-reference-{merges.txt,vocab.json} decoded to bytes
   pretok.json.gz       parallel_pretokenization Counters
+  pretok_a25.json.gz   serial_pretokenization / pretokenize(training=False) Counters, strict-decode errors (`gen_golden.py a25` makes only this one)
   train.json.gz        (vocab, merges) of train_bpe / BPETrainer.train, incl. vocab sizes where the reference
                        departs from textbook BPE and seeded synthetic corpora
   encode.json.gz       BPETokenizer.encode / encode_iterable ids (plus offline-tiktoken ids for GPT-2 cases)
@@ -77,7 +78,62 @@ INLINE = {
 }
 
 
+def gen_a25(texts, synth_data):
+    """pretok_a25.json.gz: the public wrappers of SURVEY.md §8 row A25 — serial_pretokenization (four chunks,
+    STRICT decode, pretokenization.py:255-298) and pretokenize(..., training=False) (special tokens kept as parts and
+    then pretokenized like any text, :198-207, :231) — run from the unmodified reference."""
+    H.load()
+    from bpe_transformer.tokenization.preprocessing.pretokenization import pretokenize, serial_pretokenization
+
+    def get_bytes(key: str) -> bytes:
+        if key.startswith("dirty:"):
+            base = get_bytes(key[len("dirty:"):])
+            return base[:1000] + b"\xff\xfe" + base[1000:2000] + b"\xe4\xbd" + base[2000:]
+        return synth_data[key] if key.startswith("synth:") else bytes.fromhex(texts[key])
+
+    rows = []
+    for key, fn, training, parallel, specials, workers in [
+        ("tinystories_sample.txt", "serial", True, None, [EOT], None),
+        ("tinystories_sample.txt", "serial", True, None, [], None),
+        ("corpus.en", "serial", True, None, [EOT], None),
+        ("synth:ts:5:300000", "serial", True, None, [EOT], None),
+        ("synth:owt:4:300000", "serial", False, None, [EOT], None),
+        ("tinystories_sample.txt", "pretokenize", False, True, [EOT], 4),
+        ("tinystories_sample.txt", "pretokenize", False, False, [EOT], 4),
+        ("tinystories_sample.txt", "pretokenize", True, False, [EOT], 4),
+        ("inline:overlap_specials", "pretokenize", False, True, [EOT, EOT + EOT], 1),
+        ("inline:unicode_specials", "pretokenize", False, False, [EOT], 1),
+        ("synth:ts:5:300000", "pretokenize", False, True, [EOT], 4),
+        ("dirty:synth:ts:5:300000", "serial", True, None, [EOT], None),
+        ("dirty:synth:ts:5:300000", "pretokenize", True, False, [EOT], 4),
+        ("dirty:synth:ts:5:300000", "pretokenize", True, True, [EOT], 4),
+        ("dirty:synth:ts:5:300000", "pretokenize", False, True, [EOT], 4),
+    ]:
+        tf = tempfile.NamedTemporaryFile(suffix=".txt", delete=False)
+        tf.write(get_bytes(key))
+        tf.close()
+        row = {"input": key, "fn": fn, "training": training, "parallel": parallel, "specials": specials, "n_workers": workers}
+        try:
+            if fn == "serial":
+                c = serial_pretokenization(file_path=tf.name, training=training, special_tokens=specials)
+            else:
+                c = pretokenize(file_path=tf.name, training=training, parallel_processing=parallel, n_workers=workers, special_tokens=specials)
+            row["counts"] = sorted([bytes(k).hex(), v] for k, v in c.items())
+        except UnicodeDecodeError:
+            row["raises"] = "UnicodeDecodeError"
+        os.unlink(tf.name)
+        rows.append(row)
+        print("a25", key, fn, training, parallel, row.get("raises", len(row.get("counts", []))))
+    dump("pretok_a25.json.gz", rows)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "a25":
+        import gzip as _gz
+        with _gz.open(OUT / "texts.json.gz", "rb") as fh:
+            texts = json.load(fh)
+        gen_a25(texts, {"synth:ts:5:300000": synth(0, 5, 300_000), "synth:owt:4:300000": synth(1, 4, 300_000)})
+        return
     ref = H.load()
     from bpe_transformer.tokenization.bpe_tokenizer import BPETokenizer
     from bpe_transformer.tokenization.bpe_trainer import BPETrainer
@@ -140,6 +196,8 @@ def main():
         pretok.append({"input": key, "specials": specials, "n_workers": workers,
                        "counts": sorted([bytes(k).hex(), v] for k, v in c.items())})
     dump("pretok.json.gz", pretok)
+
+    gen_a25(texts, synth_data)
 
     # ---- training -----------------------------------------------------------------------------
     train = []

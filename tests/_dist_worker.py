@@ -45,10 +45,12 @@ def main():
     lo, hi = offs[rank], offs[rank + 1]
     mine = c_oracle.count(data[lo:hi], [EOT])
     merged: Counter = Counter()
-    for blob, off, ln, cnt in D.all_gather_tables(*table_tensors(mine)):
-        b = blob.numpy().tobytes()
-        for o, l, c in zip(off.tolist(), ln.tolist(), cnt.tolist()):
-            merged[tuple(b[o:o + l])] += c
+    gathered, stride, sizes = D.all_gather_tables(*table_tensors(mine))
+    assert len(sizes) == world and sizes[rank][0] == len(mine) and gathered.numel() == stride * world and stride % 16 == 0
+    blob, off, ln, cnt = D.unpack_tables(gathered, stride, sizes)  # what ONE bpe_unique_import call is given
+    b = blob.numpy().tobytes()
+    for o, l, c in zip(off.tolist(), ln.tolist(), cnt.tolist()):
+        merged[tuple(b[o:o + l])] += c
     whole = c_oracle.count(data, [EOT])
     line_offs = D.line_shard_offsets(path, world)
     ok_lines = all(o == 0 or o == len(data) or data[o - 1:o] == b"\n" for o in line_offs) and line_offs == sorted(line_offs)

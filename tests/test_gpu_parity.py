@@ -22,6 +22,7 @@ pytestmark = pytest.mark.gpu
 PRETOK = load_golden("pretok.json.gz")
 TRAIN = load_golden("train.json.gz")
 ENCODE = load_golden("encode.json.gz")
+A25 = load_golden("pretok_a25.json.gz")
 
 
 @pytest.fixture(scope="module")
@@ -143,9 +144,32 @@ def test_counts_match_reference_golden(engine, case, input_bytes, tmp_file):
     want = Counter({tuple(bytes.fromhex(h)): c for h, c in case["counts"]})
     if case["specials"] or case["n_workers"] == 1:
         assert gpu_counter(engine, data, case["specials"]) == want
-    if case["n_workers"] <= 4:  # cpu_count() clamps n_workers; the box has more than 4 cores
-        got = parallel_pretokenization(file_path=tmp_file(data), n_workers=case["n_workers"], special_tokens=case["specials"])
-        assert got == want
+    if not case["specials"] and case["n_workers"] > (os.cpu_count() or 1):
+        pytest.skip("without special tokens the result depends on the worker count, which cpu_count() clamps on this box")
+    got = parallel_pretokenization(file_path=tmp_file(data), n_workers=case["n_workers"], special_tokens=case["specials"])
+    assert got == want
+
+
+@pytest.mark.parametrize("case", A25, ids=lambda c: f"{c['input']}-{c['fn']}-{'train' if c['training'] else 'keep'}-{c['parallel']}-{len(c['specials'])}sp")
+def test_public_pretokenize_wrappers_match_reference_golden(case, input_bytes, tmp_file):
+    """serial_pretokenization (strict decode -> UnicodeDecodeError, pretokenization.py:284) and
+    pretokenize(..., training=False) (special tokens kept as parts and pretokenized like text, :198-207, :231)."""
+    from bpe_transformer_b200.tokenization.preprocessing import pretokenize, serial_pretokenization
+    from test_oracle_pinned import a25_input
+
+    path = tmp_file(a25_input(input_bytes, case["input"]))
+
+    def run():
+        if case["fn"] == "serial":
+            return serial_pretokenization(file_path=path, training=case["training"], special_tokens=case["specials"])
+        return pretokenize(file_path=path, training=case["training"], parallel_processing=case["parallel"],
+                           n_workers=case["n_workers"], special_tokens=case["specials"])
+
+    if case.get("raises"):
+        with pytest.raises(UnicodeDecodeError):
+            run()
+    else:
+        assert run() == Counter({tuple(bytes.fromhex(h)): c for h, c in case["counts"]})
 
 
 @pytest.mark.parametrize("style,seed,size", [(0, 11, 8_000_000), (1, 12, 8_000_000)])
@@ -396,6 +420,56 @@ def ct_decode(vocab, ids):
     return b"".join(vocab[i] for i in ids).decode("utf-8", errors="replace")
 
 
+def test_two_tokenizers_of_equal_size_do_not_share_a_loaded_model(tmp_path):
+    """The engine keeps the last loaded model and skips reloading it for the same tokenizer object.  Two tokenizers with
+    equal vocabulary and merge counts but different merges, created one after the other (the first one freed, so that
+    CPython may hand its address to the second), must each encode with their own merges."""
+    import gc
+
+    from adapters import get_tokenizer, run_train_bpe
+
+    texts = []
+    models = []
+    for seed in (101, 102):
+        path = synth_corpus(1, seed, 400_000, str(tmp_path / f"c{seed}.txt"))
+        models.append(run_train_bpe(path, 700, [EOT]))
+        texts.append(open(path, encoding="utf-8").read()[:100_000])
+    assert models[0][1] != models[1][1] and len(models[0][1]) == len(models[1][1])
+    probe = texts[0][:50_000] + texts[1][:50_000]
+
+    def encode_with(k):
+        tok = get_tokenizer(*models[k], [EOT])
+        return tok.encode(probe)
+
+    for _ in range(3):
+        got = []
+        for k in (0, 1):
+            got.append(encode_with(k))
+            gc.collect()
+        for k in (0, 1):
+            assert got[k] == port.PortTokenizer(*models[k], [EOT]).encode(probe)
+
+
+def test_token_byte_pool_grows_when_tokens_get_long(tmp_file, monkeypatch):
+    """Runs of one character double the length of the newest token with every merge; the trainer's pool of token
+    byte strings is then too small, the loop stops and training runs again with a larger pool: same merges as the oracle."""
+    from adapters import run_train_bpe
+
+    data = (b"a" * 3000 + b" " + b"ab" * 700 + b"\n") * 3 + b"the end of it"
+    want = c_oracle.train(c_oracle.count(data, [EOT]), 290, [EOT])
+    assert max(len(v) for v in want[0].values()) > 512
+    monkeypatch.setenv("BPE_B200_TRAIN_BLOB_PER_TOKEN", "4")
+    assert run_train_bpe(tmp_file(data), 290, [EOT]) == want
+
+
+def test_unicode_tables_match_the_regex_on_this_box():
+    """The parity target is the `regex` module installed where the CPU baseline runs: the class
+    tables compiled into the library must be the ones that module gives, on the GPU box too."""
+    from test_oracle_pinned import test_unicode_tables_match_installed_regex
+
+    test_unicode_tables_match_installed_regex()
+
+
 def test_encode_keyerror_is_raised_every_time(gpt2_model):
     """A pretoken that cannot be encoded is not cached as if it had been: the reference raises on every call."""
     from adapters import get_tokenizer
@@ -404,10 +478,15 @@ def test_encode_keyerror_is_raised_every_time(gpt2_model):
     small = {k: v for k, v in vocab.items() if v != b"z"}
     tok = get_tokenizer(small, merges, None)
     fine = tok.encode("a plain sentence")
-    for _ in range(3):
+    for k in range(3):
         with pytest.raises(KeyError):
             tok.encode("a plain zebra sentence")
         assert tok.encode("a plain sentence") == fine
+        # pretokens the cache has not seen, after a failed call: the failed one must not block or corrupt them
+        fresh = f"brand new words number{k} arrive quietly"
+        assert tok.encode(fresh) == c_oracle.COracleTokenizer(small, merges, None).encode(fresh)
+        with pytest.raises(KeyError):
+            tok.encode(fresh + " zoo")
 
 
 def test_pipelined_file_paths_match_whole_file_paths(tmp_path, ts10k_model, monkeypatch):

@@ -90,3 +90,50 @@ def test_host_split_on_special_tokens_matches_regex_split():
         assert split_on_special_tokens(text, training=True, special_tokens=specials) == regex.split(pattern, text)
         assert split_on_special_tokens(text, training=False, special_tokens=specials) == regex.split(f"({pattern})", text)
     assert split_on_special_tokens("abc", special_tokens=None) == ["abc"]
+
+
+def test_shard_pieces_are_cut_at_special_token_starts(tmp_path):
+    from bpe_transformer_b200.distributed import _pieces_at_special_starts
+
+    rng = random.Random(5)
+    words = [b"one ", b"two ", b"three\n", EOT.encode(), b"<|other|>", b"<", b"<|"]
+    for trial in range(60):
+        data = b"".join(rng.choice(words) for _ in range(rng.randint(1, 5000)))
+        path = tmp_path / "f.txt"
+        path.write_bytes(data)
+        lo = rng.randint(0, len(data) // 2)
+        hi = rng.randint(lo, len(data))
+        specials = [EOT] if trial % 2 else [EOT, "<|other|>"]
+        offs = _pieces_at_special_starts(str(path), lo, hi, rng.choice([1, 50, 700, 100000]), specials)
+        assert offs[0] == lo and offs[-1] == hi and offs == sorted(offs)
+        assert len(set(offs[:-1])) == len(offs[:-1])
+        needles = [s.encode() for s in specials]
+        assert all(any(data[o:o + len(nd)] == nd for nd in needles) for o in offs[1:-1])
+
+
+def test_packed_table_exchange_layout_round_trips():
+    """pack_table / unpack_tables without a process group: two ranks' payloads laid out as the all-gather would."""
+    import numpy as np
+    import torch
+
+    from bpe_transformer_b200 import distributed as D
+
+    def table(words):
+        blob = b"".join(words)
+        lens = np.asarray([len(w) for w in words], dtype=np.int32)
+        off = np.zeros(len(words), dtype=np.int64)
+        off[1:] = np.cumsum(lens[:-1])
+        return (torch.from_numpy(np.frombuffer(blob, dtype=np.uint8).copy()), torch.from_numpy(off), torch.from_numpy(lens),
+                torch.arange(1, len(words) + 1, dtype=torch.int64))
+
+    tables = [table([b" the", b"a", b" longer word"]), table([b"x" * 37])]
+    packed = [D.pack_table(*t) for t in tables]
+    sizes = [(n, nb) for _, n, nb in packed]
+    stride = (max(D.payload_bytes(*sz) for sz in sizes) + 63) // 64 * 64 + 64
+    gathered = torch.zeros(stride * 2, dtype=torch.uint8)
+    for r, (payload, _, _) in enumerate(packed):
+        gathered[r * stride:r * stride + payload.numel()] = payload
+    blob, off, ln, cnt = D.unpack_tables(gathered, stride, sizes)
+    raw = blob.numpy().tobytes()
+    got = [(raw[o:o + l], c) for o, l, c in zip(off.tolist(), ln.tolist(), cnt.tolist())]
+    assert got == [(b" the", 1), (b"a", 2), (b" longer word", 3), (b"x" * 37, 1)]

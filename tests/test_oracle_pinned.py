@@ -20,6 +20,15 @@ from conftest import EOT, expand_row, load_golden, with_specials
 PRETOK = load_golden("pretok.json.gz")
 TRAIN = load_golden("train.json.gz")
 ENCODE = load_golden("encode.json.gz")
+A25 = load_golden("pretok_a25.json.gz")
+
+
+def a25_input(input_bytes, key: str) -> bytes:
+    """Inputs of tests/golden/pretok_a25.json.gz ("dirty:" = invalid UTF-8 spliced in, as oracle/gen_golden.py does)."""
+    if key.startswith("dirty:"):
+        base = input_bytes(key[len("dirty:"):])
+        return base[:1000] + b"\xff\xfe" + base[1000:2000] + b"\xe4\xbd" + base[2000:]
+    return input_bytes(key)
 
 
 def _counter(rows):
@@ -35,6 +44,18 @@ def test_pretoken_counts_match_reference(case, input_bytes, tmp_file):
     if case["specials"] or case["n_workers"] == 1:
         # the C oracle has no worker chunking; with specials (or one worker) chunk cuts cannot matter
         assert c_oracle.count(data, case["specials"]) == want
+
+
+@pytest.mark.parametrize("case", [c for c in A25 if c["fn"] == "serial" and c["training"]],
+                         ids=lambda c: f"{c['input']}-{len(c['specials'])}sp")
+def test_serial_pretokenization_matches_reference(case, input_bytes, tmp_file):
+    """four chunks, strict decode (pretokenization.py:255-298)."""
+    path = tmp_file(a25_input(input_bytes, case["input"]))
+    if case.get("raises"):
+        with pytest.raises(UnicodeDecodeError):
+            port.count_pretokens_serial(path, case["specials"])
+    else:
+        assert port.count_pretokens_serial(path, case["specials"]) == _counter(case["counts"])
 
 
 @pytest.mark.parametrize("case", TRAIN, ids=lambda c: f"{c['input']}-{c['vocab_size']}")
