@@ -13,8 +13,10 @@ token-start scan -> distinct-pretoken count -> (N > 1: all-gather of the tables)
              memory -> HBM -> kernels -> merges back on the host, all inside the timed region
   encode     the second half of the metric: GB/s of corpus through BPETokenizer (resident and end to end)
   roofline   the slower of the two HBM-bound kernels of a step (scan / count): algorithmic bytes = corpus bytes
-  cpu_baseline  oracle/bpe_ref_port.py (the reference's algorithm, regex + Counter + heap, all host cores) on a
-             bounded sample, extrapolated to the workload
+  cpu_baseline  oracle/bpe_ref_port.py (the reference's algorithm, regex + Counter + heap, all host cores) over the
+             WHOLE corpus, one measured run; its pretoken Counter, vocab and merges are compared with the GPU's
+  parity     the gate: merges / vocab / Counter equal the CPU run's, ids equal the C oracle's over the whole corpus and
+             the port's over a 64 MB prefix; sha256 of merges and ids at every N.  Any mismatch: exit code 3
 The corpus (2.1 GB) is far larger than L2 (126 MB), so no L2 flush is needed between iterations.
 """
 from __future__ import annotations
@@ -368,7 +370,6 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
         vocab, merges = train_e2e()
     sync_all()
     e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
-    assert merges == tr.merges
     log(f"[bench] train end to end: {e2e_s:.3f} s/call")
 
     # ---- encode: configs[3] ------------------------------------------------------------------------------------
@@ -495,14 +496,72 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
         "distinct_pretokens": int(n_unique), "pretokens": int(n_tokens), "merges": len(merges),
         "kernels": kernels, "clocks": clocks,
     }
+    # ---- the results themselves: hashes at every N (the N-GPU merges and ids must equal the 1-GPU ones) --------------
+    import hashlib
+
+    ids_host = _lib.host_array(n_ids_local, np.uint16)
+    eng.store_into(ids, ids_host)
+    ids_sha = None
+    if world == 1:
+        ids_sha = hashlib.sha256(ids_host.tobytes()).hexdigest()
+    else:  # the ranks' ids in rank order, through files on this box (one node): rank 0 hashes the concatenation
+        part = f"{path}.ids.rank{rank}"
+        ids_host.tofile(part)
+        dist.barrier()
+        if rank == 0:
+            h = hashlib.sha256()
+            for r in range(world):
+                with open(f"{path}.ids.rank{r}", "rb") as fh:
+                    while True:
+                        block = fh.read(64 << 20)
+                        if not block:
+                            break
+                        h.update(block)
+            ids_sha = h.hexdigest()
+        dist.barrier()
+        os.unlink(part)
+    parity = {"merges_sha256": merges_sha256(merges), "ids_sha256": ids_sha, "resident_merges_equal_e2e_merges": merges == tr.merges,
+              "roundtrip_decode_equals_input": roundtrip_ok}
+    line["parity"] = parity
+    failed = [k for k in ("resident_merges_equal_e2e_merges", "roundtrip_decode_equals_input") if not parity[k]]
+
+    # ---- CPU side, same run, same box: the reference's algorithm over the WHOLE corpus, and the parity gate -------------
     if rank == 0 and world == 1 and not args.no_cpu:
+        from collections import Counter
+
+        from bpe_transformer_b200.tokenization.preprocessing.pretokenization import counter_from_engine
+
         t0 = time.perf_counter()
-        line["cpu_baseline"] = cpu_train_sample(path, total, min(total, args.cpu_sample_bytes))
-        line["encode"]["cpu_baseline"] = cpu_encode_sample(path, vocab, merges, min(total, args.cpu_sample_bytes // 8))
-        log(f"[bench] cpu baseline: train {line['cpu_baseline']['value']:.1f} s, encode {line['encode']['cpu_baseline']['value'] * 1e3:.2f} MB/s "
-            f"({time.perf_counter() - t0:.1f} s)")
+        full = cpu_train_full(path)
+        line["cpu_baseline"] = {k: v for k, v in full.items() if not k.startswith("_")}
+        log(f"[bench] cpu baseline (full corpus, measured): train {full['value']:.1f} s")
+        parity["oracle"] = "oracle/bpe_ref_port.py (the reference's algorithm) over the whole corpus; ids: oracle/bpe_oracle.c over the whole corpus + the port on a prefix"
+        parity["merges_equal"] = merges == full["_merges"]
+        parity["vocab_equal"] = vocab == full["_vocab"]
+        parity["cpu_merges_sha256"] = merges_sha256(full["_merges"])
+        eng.unique_reset()
+        eng.count(d_text, n_local, eng.scan(d_text, n_local))
+        parity["pretoken_counter_equal"] = counter_from_engine(eng) == Counter(full["_counter"])
+        # ids: the C oracle over the whole corpus (threads over line ranges), the port over a prefix (also the timed baseline)
+        c_sha, c_n = c_oracle_ids_sha256(path, vocab, merges)
+        parity["ids_equal_full_corpus"] = (c_sha == ids_sha and c_n == n_ids_local)
+        parity["cpu_ids_sha256"] = c_sha
+        enc_cpu = cpu_encode_sample(path, vocab, merges, min(total, args.cpu_sample_bytes), min(total, 2_000_000))
+        ref_ids = enc_cpu.pop("_ids_serial")
+        enc_cpu.pop("_serial_bytes")
+        parity["ids_equal_first_64MB"] = bool(ref_ids.size <= ids_host.size and np.array_equal(ids_host[:ref_ids.size].astype(np.uint32), ref_ids))
+        line["encode"]["cpu_baseline"] = enc_cpu
+        line["encode_vs_cpu"] = {"gpu_e2e_GBps": line["encode"]["e2e"]["value"], "cpu_GBps": enc_cpu["value"], "cpu_variant": enc_cpu["variant"],
+                                 "ratio": line["encode"]["e2e"]["value"] / enc_cpu["value"]}
+        failed += [k for k in ("merges_equal", "vocab_equal", "pretoken_counter_equal", "ids_equal_full_corpus", "ids_equal_first_64MB") if not parity[k]]
+        log(f"[bench] parity vs the CPU run: " + ", ".join(f"{k}={parity[k]}" for k in ("merges_equal", "vocab_equal", "pretoken_counter_equal",
+                                                                                          "ids_equal_full_corpus", "ids_equal_first_64MB"))
+            + f"; cpu encode {enc_cpu['value'] * 1e3:.2f} MB/s ({enc_cpu['variant']}); CPU side took {time.perf_counter() - t0:.1f} s")
     if rank == 0:
         print(json.dumps(line), flush=True)
+    if failed:
+        log(f"[bench] PARITY FAILED: {failed}")
+        raise SystemExit(3)
 
 
 def main():
@@ -513,7 +572,8 @@ def main():
     ap.add_argument("--bytes", type=int, default=int(os.environ.get("BPE_BENCH_BYTES", 2_100_000_000)))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample-bytes", type=int, default=64_000_000)
-    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline and the parity gate against it")
+    ap.add_argument("--no-cpu-encode", action="store_true", help="--impl reference: skip the CPU encode timings")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     rank = int(os.environ.get("RANK", "0"))
