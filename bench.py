@@ -7,7 +7,7 @@ corpus) and encode GB/s, next to the reference's CPU path timed on the same box.
         bench.py --gpus N --steps K --warmup W
 
 One JSON line on stdout (rank 0).  A "step" is one full pass of the training hot path over the corpus:
-token-start scan -> distinct-pretoken count -> (N > 1: all-gather of the tables) -> pair histogram -> merge loop.
+split + hash + count of the pretokens (one kernel) -> (N > 1: all-gather of the tables) -> pair histogram -> merge loop.
   value      seconds per step with the corpus already resident in HBM (CUDA events, max over ranks)
   e2e        seconds per call of the public API train_bpe(path, 10000, ["<|endoftext|>"]) — file -> pinned host
              memory -> HBM -> kernels -> merges back on the host, all inside the timed region
@@ -328,8 +328,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
 
     def train_step_resident():
         eng.unique_reset()
-        mask = eng.scan(d_text, n_local)
-        eng.count(d_text, n_local, mask)
+        eng.pretokenize_count(d_text, n_local)
         if world > 1:
             D.exchange_unique(eng)
         tr = BPETrainer(vocab_size=VOCAB_SIZE, special_tokens=specials)
@@ -454,7 +453,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
         kernels[name] = {"ms": ms, "launches": n}
     for name, (ms, n) in k_enc.items():
         kernels["encode:" + name] = {"ms": ms, "launches": n}
-    hbm_kernels = {k: gbps(n_local, k_train[k][0]) for k in ("scan_kernel", "count_kernel") if k in k_train and k_train[k][0]}
+    hbm_kernels = {k: gbps(n_local, k_train[k][0]) for k in ("fused_count_kernel", "scan_kernel", "count_kernel") if k in k_train and k_train[k][0]}
     dominant = min(hbm_kernels, key=hbm_kernels.get) if hbm_kernels else None
     # DRAM bytes per launch from the committed `ncu --set full` capture (tools/ncu_summary.py); only quoted for the
     # corpus size it was taken on, one GPU.
@@ -462,7 +461,8 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
     ncu_traffic = {}
     if traffic_file.exists() and world == 1 and abs(total - 2_100_000_403) < 1_000_000:
         ncu_traffic = json.loads(traffic_file.read_text())
-    ncu_name = {"scan_kernel": "scan_kernel<0>", "count_kernel": "count_kernel", "emit_fused_kernel": "emit_fused_kernel<unsigned short>"}
+    ncu_name = {"scan_kernel": "scan_kernel<0>", "count_kernel": "count_kernel", "emit_fused_kernel": "emit_fused_kernel<unsigned short>",
+                "fused_count_kernel": "fused_count_kernel<0, 0>", "fused_emit_kernel": "fused_emit_kernel"}
     roofline = None
     if dominant:
         others = {k: {"achieved": v, "frac": v / peak, "traffic": ncu_traffic.get(ncu_name[k])} for k, v in hbm_kernels.items() if k != dominant}
@@ -540,7 +540,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
         parity["vocab_equal"] = vocab == full["_vocab"]
         parity["cpu_merges_sha256"] = merges_sha256(full["_merges"])
         eng.unique_reset()
-        eng.count(d_text, n_local, eng.scan(d_text, n_local))
+        eng.pretokenize_count(d_text, n_local)
         parity["pretoken_counter_equal"] = counter_from_engine(eng) == Counter(full["_counter"])
         # ids: the C oracle over the whole corpus (threads over line ranges), the port over a prefix (also the timed baseline)
         c_sha, c_n = c_oracle_ids_sha256(path, vocab, merges)

@@ -26,7 +26,7 @@ SYMBOLS = [
     "bpe_ctx_create", "bpe_ctx_destroy", "bpe_last_error", "bpe_ctx_configure", "bpe_set_special_tokens", "bpe_scan",
     "bpe_count", "bpe_unique_stats", "bpe_unique_export", "bpe_unique_import", "bpe_unique_reset", "bpe_train",
     "bpe_train_timing", "bpe_load_model", "bpe_encode", "bpe_decode", "bpe_kernel_times", "bpe_set_profiling",
-    "bpe_decode_noalloc", "bpe_load_file", "bpe_store_to_host", "bpe_load_file_ranges",
+    "bpe_decode_noalloc", "bpe_load_file", "bpe_store_to_host", "bpe_load_file_ranges", "bpe_pretokenize_count",
 ]
 
 
@@ -68,6 +68,7 @@ def load_library():
         lib.bpe_set_special_tokens.argtypes = [vp, u8p, u32p, C.c_int]
         lib.bpe_scan.argtypes = [vp, u8p, C.c_uint64, u64p, C.c_uint64, C.c_uint32, u32p, vp]
         lib.bpe_count.argtypes = [vp, u8p, C.c_uint64, u32p, vp]
+        lib.bpe_pretokenize_count.argtypes = [vp, u8p, C.c_uint64, u64p, C.c_uint64, C.c_uint32, u32p, vp]
         lib.bpe_unique_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         lib.bpe_unique_export.argtypes = [vp, u8p, u64p, u32p, u64p, vp]
         lib.bpe_unique_import.argtypes = [vp, u8p, u64p, u32p, u64p, C.c_uint64, vp]
@@ -248,6 +249,18 @@ class Engine:
 
     def count(self, d_text, n: int, mask):
         self._check(self.lib.bpe_count(self.ctx, d_text.data_ptr(), n, mask.data_ptr(), self._stream()))
+
+    def pretokenize_count(self, d_text, n: int, cuts=None, flags: int = 0, want_mask: bool = False):
+        """scan + count in one pass (bpe_pretokenize_count); returns the start mask if asked for, else None."""
+        torch = self.torch
+        mask = self.new_mask(n) if want_mask else None
+        d_cuts, n_cuts = None, 0
+        if cuts is not None and len(cuts):
+            d_cuts = torch.as_tensor(np.asarray(cuts, dtype=np.int64), device=f"cuda:{self.device}")
+            n_cuts = int(d_cuts.numel())
+        self._check(self.lib.bpe_pretokenize_count(self.ctx, d_text.data_ptr(), n, d_cuts.data_ptr() if d_cuts is not None else None, n_cuts,
+                                                   flags, mask.data_ptr() if mask is not None else None, self._stream()))
+        return mask
 
     def unique_stats(self) -> tuple[int, int, int]:
         a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()

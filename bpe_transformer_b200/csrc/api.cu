@@ -154,6 +154,8 @@ int bpe_set_special_tokens(bpe_ctx* ctx, const uint8_t* h_blob, const uint32_t* 
         sp.off[k] = h_off[k] - h_off[0];
         sp.off[k + 1] = h_off[k + 1] - h_off[0];
         memcpy(sp.blob + sp.off[k], h_blob + h_off[k], len);
+        memcpy(sp.words[k], h_blob + h_off[k], len);  // little-endian words, zero padded (memset above)
+        if (len > 1 && memchr(h_blob + h_off[k], '\n', len - 1)) sp.newline_inside |= 1u << k;
         uint8_t b0 = h_blob[h_off[k]];
         sp.first_byte_mask[b0 >> 5] |= 1u << (b0 & 31);
         sp.max_len = std::max<int>(sp.max_len, (int)len);
@@ -186,6 +188,25 @@ int bpe_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d
     int rc = ensure_unique(ctx);
     if (rc) return rc;
     rc = launch_count(ctx, d_text, n, d_start, s);
+    if (rc) return rc;
+    return ctx_status_to_code(ctx, ctx_read_status(ctx, s));
+}
+
+int bpe_pretokenize_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint64_t* d_cuts, uint64_t n_cuts, uint32_t flags,
+                          uint32_t* d_start, void* stream) {
+    if (!ctx || (n && !d_text) || ((uintptr_t)d_text & 15)) return ctx ? ctx_fail(ctx, BPE_ERR_ARGUMENT, "bpe_pretokenize_count arguments") : BPE_ERR_ARGUMENT;
+    cudaStream_t s = (cudaStream_t)stream;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    int rc = ensure_unique(ctx);
+    if (rc) return rc;
+    uint32_t* cutmask = nullptr;
+    if (d_cuts && n_cuts) {
+        cutmask = (uint32_t*)ctx_scratch(ctx, 5, (n / 32 + 2) * 4);
+        if (!cutmask) return BPE_ERR_CUDA;
+        rc = launch_cuts_to_mask(ctx, d_cuts, n_cuts, n, cutmask, s);
+        if (rc) return rc;
+    }
+    rc = launch_fused_count(ctx, d_text, n, cutmask, flags, d_start, s);
     if (rc) return rc;
     return ctx_status_to_code(ctx, ctx_read_status(ctx, s));
 }

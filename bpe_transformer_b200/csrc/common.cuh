@@ -48,33 +48,41 @@ struct Specials {
     int max_len;
     uint32_t off[BPE_MAX_SPECIALS + 1];
     uint32_t first_byte_mask[8];  // 256-bit set of first bytes
+    uint32_t newline_inside;      // bit s: token s holds a '\n' before its last byte (a cut after every newline splits it)
     uint8_t blob[BPE_MAX_SPECIAL_BYTES];
+    unsigned long long words[BPE_MAX_SPECIALS][8];  // token s as little-endian 64-bit words, zero padded (at most 60 bytes)
 };
 
-// Index of the first special token (priority order) that matches text at p and fits below `limit`; -1 if none.
-__device__ __forceinline__ int special_at(const Specials& sp, const uint8_t* __restrict__ text, uint64_t p, uint64_t limit) {
-    uint8_t b0 = text[p];
-    if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return -1;
-    for (int s = 0; s < sp.n; s++) {
-        uint32_t len = sp.off[s + 1] - sp.off[s];
-        if (p + len > limit) continue;
-        bool ok = true;
-        for (uint32_t k = 0; k < len && ok; k++) ok = text[p + k] == sp.blob[sp.off[s] + k];
-        if (ok) return s;
-    }
-    return -1;
+// ---- the 64-bit key of a byte string ------------------------------------------------------------------------------
+// Internal to the library (the oracle compares byte strings, never hashes).  The key is a finalised polynomial
+// hash: H(b_0 .. b_{L-1}) = sum b_j R^(L-1-j) mod 2^64, i.e. Horner's rule one byte at a time.  That form is what lets
+// the fused kernels (fused.cu) hash every token of a text in one sweep: a lane runs Horner over its own 32 bytes,
+// restarting at token starts, and a token that spans lanes is put together from the pieces as H_left * R^n + H_right.
+// Every path that names a pretoken by key (count, import, encode lookup) uses the same function.
+#define BPE_HASH_R 0x9E3779B1u  // odd, 32 bits: h * R + b is one wide multiply-add and one multiply-add
+
+__device__ __forceinline__ uint64_t poly_step(uint64_t h, uint32_t b) {
+    const uint64_t t = (uint64_t)(uint32_t)h * BPE_HASH_R + b;
+    return ((uint64_t)((uint32_t)(h >> 32) * BPE_HASH_R + (uint32_t)(t >> 32)) << 32) | (uint32_t)t;
 }
 
-// ---- 64-bit key + 32-bit check of a byte string ---------------------------------------------------------
-// Internal to the library (the oracle compares byte strings, never hashes).  Eight bytes per round.
-__device__ __forceinline__ uint64_t mix64(uint64_t h, uint64_t w) {
-    h = (h ^ w) * 0x9FB21C651E98DF25ull;
-    return h ^ (h >> 35);
+// h * R^k for the combination of pieces (k is small on the paths that call this: one step per byte).
+__device__ __forceinline__ uint64_t poly_shift(uint64_t h, uint64_t k) {
+    uint64_t r = BPE_HASH_R, acc = 1;
+    for (; k; k >>= 1) {
+        if (k & 1) acc *= r;
+        r *= r;
+    }
+    return h * acc;
 }
-__device__ __forceinline__ uint32_t mix32(uint32_t h, uint64_t w) {
-    h = (h ^ (uint32_t)w) * 0x85EBCA6Bu;
-    h = (h ^ (uint32_t)(w >> 32) ^ (h >> 15)) * 0xC2B2AE35u;
-    return h ^ (h >> 13);
+
+// Never 0 (0 marks an empty slot).  A bijection of H + len * C apart from 0 -> 1.
+__device__ __forceinline__ uint64_t key_finalize(uint64_t h, uint64_t len) {
+    uint64_t k = h + len * 0x9E3779B97F4A7C15ull;
+    k ^= k >> 32;
+    k *= 0xD6E8FEB86659FD93ull;
+    k ^= k >> 29;
+    return k ? k : 1ull;
 }
 
 // Unaligned little-endian 64-bit read through two aligned reads (the buffer is padded: BPE_TEXT_PAD).
@@ -89,38 +97,43 @@ __device__ __forceinline__ uint64_t load_u64_unaligned(const uint8_t* __restrict
 
 struct TokenKey {
     uint64_t key;  // never 0
-    uint32_t chk;  // never 0
 };
 
-__device__ __forceinline__ TokenKey hash_bytes(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
-    uint64_t h = 0x243F6A8885A308D3ull ^ (len * 0x9E3779B97F4A7C15ull);
-    uint32_t c = 0x13198A2Eu ^ (uint32_t)len;
-    uint64_t o = 0;
+// text[p, p + len) == special token s ?  Eight bytes per compare (the text buffer is padded, so the last word may be read whole).
+__device__ __forceinline__ bool special_equals(const Specials& sp, int s, const uint8_t* __restrict__ text, uint64_t p, uint32_t len) {
+    bool ok = true;
+#pragma unroll 1
+    for (uint32_t k = 0; 8 * k < len && ok; k++) {
+        uint64_t w = load_u64_unaligned(text, p + 8 * k);
+        if (8 * k + 8 > len) w &= (1ull << (8 * (len - 8 * k))) - 1ull;
+        ok = w == sp.words[s][k];
+    }
+    return ok;
+}
+
+__device__ __forceinline__ uint64_t poly_hash(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
+    uint64_t h = 0, o = 0;
+#pragma unroll 1
     for (; o + 8 <= len; o += 8) {
         uint64_t w = load_u64_unaligned(base, p + o);
-        h = mix64(h, w);
-        c = mix32(c, w);
+#pragma unroll
+        for (int k = 0; k < 8; k++) h = poly_step(h, (uint32_t)(w >> (8 * k)) & 0xFFu);
     }
     if (o < len) {
-        uint64_t w = load_u64_unaligned(base, p + o) & ((1ull << ((len - o) * 8)) - 1ull);
-        h = mix64(h, w);
-        c = mix32(c, w);
+        uint64_t w = load_u64_unaligned(base, p + o);
+        for (uint64_t k = 0; k < len - o; k++) h = poly_step(h, (uint32_t)(w >> (8 * k)) & 0xFFu);
     }
-    h ^= h >> 29;
+    return h;
+}
+
+__device__ __forceinline__ TokenKey hash_bytes(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
     TokenKey k;
-    k.key = h ? h : 1ull;
-    k.chk = c ? c : 1u;
+    k.key = key_finalize(poly_hash(base, p, len), len);
     return k;
 }
 
-// Key only (the check word is recomputed when a shared-table entry is folded into the global table).
 __device__ __forceinline__ uint64_t hash_key(const uint8_t* __restrict__ base, uint64_t p, uint32_t len) {
-    uint64_t h = 0x243F6A8885A308D3ull ^ ((uint64_t)len * 0x9E3779B97F4A7C15ull);
-    uint32_t o = 0;
-    for (; o + 8 <= len; o += 8) h = mix64(h, load_u64_unaligned(base, p + o));
-    if (o < len) h = mix64(h, load_u64_unaligned(base, p + o) & ((1ull << ((len - o) * 8)) - 1ull));
-    h ^= h >> 29;
-    return h ? h : 1ull;
+    return key_finalize(poly_hash(base, p, len), len);
 }
 
 // ---- the table of distinct pretokens (context-owned, global memory) ---------------------------------------
@@ -129,7 +142,7 @@ struct UniqueTable {
     uint64_t* cnt;       // [cap] occurrences
     uint64_t* pool_off;  // [cap] offset of the bytes in `pool`
     uint32_t* len;       // [cap]
-    uint32_t* chk;       // [cap] 0 until the inserting thread has published
+    uint32_t* chk;       // [cap] 0 until the inserting thread has published length and bytes, then 1
     uint32_t* enc_off;   // [cap] offset of the cached encoding in the id pool (encode path)
     uint32_t* enc_len;   // [cap] 0xFFFFFFFF = not encoded yet
     uint4* enc;          // [cap] what the emit pass reads, one 16-byte load per probe: {key lo, key hi, w0, w1}, key 0 = empty.
@@ -143,8 +156,18 @@ struct UniqueTable {
 
 __device__ __forceinline__ void set_status(uint32_t* status, uint32_t bit) { atomicOr(status, bit); }
 
+// Do text[p, p + len) and the pool copy of `slot` hold the same bytes?  The caller has seen chk[slot] != 0.
+__device__ __forceinline__ bool unique_same_bytes(const UniqueTable& t, uint64_t slot, const uint8_t* __restrict__ text, uint64_t p, uint64_t len) {
+    if (*reinterpret_cast<volatile uint32_t*>(t.len + slot) != (uint32_t)len) return false;
+    const volatile uint8_t* q = t.pool + *reinterpret_cast<volatile uint64_t*>(t.pool_off + slot);
+    for (uint64_t i = 0; i < len; i++)
+        if (q[i] != text[p + i]) return false;
+    return true;
+}
+
 // Adds `c` occurrences of text[p, p+len) to the table (copies the bytes into the pool on first sight).
-// Returns the slot, or ~0 when the table is full.
+// Identity is the BYTES: a key that is already present with other bytes raises ST_COLLISION (the reference's Counter
+// is keyed by the bytes themselves, pretokenization.py:201-207).  Returns the slot, or ~0 when the table is full.
 __device__ __forceinline__ uint64_t unique_insert(const UniqueTable& t, uint32_t* status, const uint8_t* __restrict__ text,
                                                   uint64_t p, uint32_t len, TokenKey k, uint64_t c) {
     uint64_t slot = (k.key * 0xD6E8FEB86659FD93ull >> 17) & t.cap_mask;
@@ -159,6 +182,7 @@ __device__ __forceinline__ uint64_t unique_insert(const UniqueTable& t, uint32_t
                 uint64_t off = atomicAdd(reinterpret_cast<unsigned long long*>(t.counters + 0), (unsigned long long)len);
                 if (off + len > t.pool_cap) {
                     set_status(status, ST_POOL_FULL);
+                    off = 0;
                 } else {
                     for (uint32_t i = 0; i < len; i++) t.pool[off + i] = text[p + i];
                 }
@@ -166,7 +190,7 @@ __device__ __forceinline__ uint64_t unique_insert(const UniqueTable& t, uint32_t
                 t.len[slot] = len;
                 t.enc_len[slot] = 0xFFFFFFFFu;
                 __threadfence();
-                *reinterpret_cast<volatile uint32_t*>(t.chk + slot) = k.chk;
+                *reinterpret_cast<volatile uint32_t*>(t.chk + slot) = 1u;
                 const unsigned long long n_before = atomicAdd(reinterpret_cast<unsigned long long*>(t.counters + 1), 1ull);
                 // beyond 7/8 full (large tables only) the probe sequences explode: stop early, the host enlarges the table
                 if (t.cap_mask >= 4096 && n_before > (t.cap_mask + 1) / 8 * 7) set_status(status, ST_TABLE_FULL);
@@ -175,8 +199,13 @@ __device__ __forceinline__ uint64_t unique_insert(const UniqueTable& t, uint32_t
             }
         }
         if (cur == k.key) {
-            uint32_t seen = *reinterpret_cast<volatile uint32_t*>(t.chk + slot);
-            if (seen != 0 && seen != k.chk) set_status(status, ST_COLLISION);
+            // the inserting thread publishes within a few hundred cycles; a reader that arrives earlier waits for it
+            uint32_t ready = 0;
+            for (int spin = 0; spin < 4096 && !(ready = *reinterpret_cast<volatile uint32_t*>(t.chk + slot)); spin++) __nanosleep(32);
+            if (ready) {
+                __threadfence();
+                if (!(*reinterpret_cast<volatile uint32_t*>(status) & ST_POOL_FULL) && !unique_same_bytes(t, slot, text, p, len)) set_status(status, ST_COLLISION);
+            }
             if (c) atomicAdd(reinterpret_cast<unsigned long long*>(t.cnt + slot), (unsigned long long)c);
             return slot;
         }
@@ -208,9 +237,7 @@ __device__ __forceinline__ int special_index(const Specials& sp, uint32_t fb, co
     } else if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return -1;
     for (int s = 0; s < sp.n; s++) {
         if (sp.off[s + 1] - sp.off[s] != len) continue;
-        bool ok = true;
-        for (uint32_t k = 0; k < len && ok; k++) ok = text[p + k] == sp.blob[sp.off[s] + k];
-        if (ok) return s;
+        if (special_equals(sp, s, text, p, (uint32_t)len)) return s;
     }
     return -1;
 }
@@ -278,6 +305,7 @@ struct bpe_ctx {
     uint64_t idpool_cap = 0;
     uint64_t enc_done = 0;             // number of distinct pretokens already encoded
     bool enc_warm = false;             // the last bpe_encode found every pretoken in the table: try without counting first
+    uint32_t fused_attr_set = 0;  // bit per variant of the fused kernels
     bool count_attr_set = false, emit_attr_set = false;  // dynamic shared memory limits raised for this device's kernels
     // scratch reused across calls
     void* scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -336,6 +364,7 @@ void io_staging_free(bpe_ctx* ctx);
 int launch_scan(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_cutmask, uint32_t flags, uint32_t* d_start, cudaStream_t s);
 int launch_cuts_to_mask(bpe_ctx* ctx, const uint64_t* d_cuts, uint64_t n_cuts, uint64_t n, uint32_t* d_cutmask, cudaStream_t s);
 int launch_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, cudaStream_t s);
+int launch_fused_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_cutmask, uint32_t flags, uint32_t* d_start, cudaStream_t s);
 int launch_import(bpe_ctx* ctx, const uint8_t* d_blob, const uint64_t* d_off, const uint32_t* d_len, const uint64_t* d_cnt,
                   uint64_t n_unique, cudaStream_t s);
 int launch_export(bpe_ctx* ctx, uint8_t* d_blob, uint64_t* d_off, uint32_t* d_len, uint64_t* d_cnt, cudaStream_t s);

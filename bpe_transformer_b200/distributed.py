@@ -178,14 +178,17 @@ def count_shard(engine: "_lib.Engine", path, lo: int, hi: int, special_tokens: l
                 raise _lib.BpeError(_lib.ERR_CAPACITY, "table of distinct pretokens cannot grow further")
     d_text, n = engine.load_file(path, lo, hi)
     try:
-        mask = engine.scan(d_text, n)
+        if not reset:
+            engine.scan(d_text, n)  # earlier shards are in the table: find invalid UTF-8 before anything of this shard is counted
+        pt.count_with_growth(engine, d_text, n, keep_counted=not reset)
     except _lib.InvalidUtf8:
         with open(path, "rb") as fh:
             fh.seek(lo)
             clean, _ = pt._sanitised(fh.read(hi - lo), [], strict=False)
+        if reset:
+            engine.unique_reset()  # the one-pass kernel had counted some of the dirty bytes before it reported them
         d_text, n = engine.to_device(clean)
-        mask = engine.scan(d_text, n)
-    pt.count_with_growth(engine, d_text, n, mask, keep_counted=not reset)
+        pt.count_with_growth(engine, d_text, n, keep_counted=not reset)
 
 
 def train_bpe_sharded(input_path, vocab_size: int, special_tokens: list[str], group=None):

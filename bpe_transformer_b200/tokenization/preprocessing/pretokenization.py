@@ -4,7 +4,8 @@
 What runs where:
   * host: read the file into pinned memory, copy it to HBM; for a corpus WITHOUT special tokens also compute
     the reference's worker chunk offsets (they are segment boundaries there and so change the result);
-  * GPU (csrc/scan.cu, csrc/count.cu): special-token split, the GPT-2 pattern, the Counter of pretokens;
+  * GPU (csrc/fused.cu; csrc/scan.cu for callers that want the start mask): special-token split, the GPT-2 pattern,
+    the Counter of pretokens, in one pass over the text;
   * host: only when a Counter is asked for, the distinct pretokens (10^4..10^7 of them) are copied back and
     turned into the reference's `Counter[tuple[int, ...], int]`.
 `n_workers` keeps its meaning for the chunk offsets only; the work itself is one GPU's.
@@ -142,13 +143,15 @@ def count_into_engine(engine: "_lib.Engine", file_path, special_tokens: list[str
                 raise _lib.BpeError(_lib.ERR_CAPACITY, "table of distinct pretokens cannot grow further")
     d_text, n = engine.load_file(file_path)
     try:
-        mask = engine.scan(d_text, n, cuts=cuts)
+        count_with_growth(engine, d_text, n, cuts, keep_counted=not reset)
     except _lib.InvalidUtf8:
+        if not reset:
+            raise  # counts of this file are already mixed into the caller's table: nothing sane to keep
         with open(file_path, "rb") as fh:
             clean, cuts = _sanitised(fh.read(), cuts, strict)
+        engine.unique_reset()  # the one-pass kernel had counted some of the dirty bytes before it reported them
         d_text, n = engine.to_device(clean)
-        mask = engine.scan(d_text, n, cuts=cuts)
-    count_with_growth(engine, d_text, n, mask)
+        count_with_growth(engine, d_text, n, cuts)
 
 
 def _count_file_pipelined(engine: "_lib.Engine", file_path, special_tokens: list[str]) -> str:
@@ -169,7 +172,7 @@ def _count_pieces_pipelined(engine: "_lib.Engine", file_path, offs: list[int]) -
         for k in range(len(offs) - 1):
             d_text, n = load.piece(k)  # blocks until piece k has landed; later pieces keep arriving meanwhile
             if n:
-                engine.count(d_text, n, engine.scan(d_text, n))
+                engine.pretokenize_count(d_text, n)
     except _lib.InvalidUtf8:
         outcome = "invalid-utf8"
     except _lib.BpeError as e:
@@ -185,12 +188,13 @@ def _count_pieces_pipelined(engine: "_lib.Engine", file_path, offs: list[int]) -
     return outcome
 
 
-def count_with_growth(engine: "_lib.Engine", d_text, n: int, mask, keep_counted: bool = False) -> None:
-    """bpe_count; if the context's table of distinct pretokens or its byte pool is too small for this corpus, enlarge
-    it (x4) and count again.  `keep_counted`: earlier shards are in the table and must not be dropped -> no retry."""
+def count_with_growth(engine: "_lib.Engine", d_text, n: int, cuts=None, keep_counted: bool = False) -> None:
+    """bpe_pretokenize_count (split + hash + count in one pass); if the context's table of distinct pretokens or its
+    byte pool is too small for this corpus, enlarge it (x4) and count again.  `keep_counted`: earlier shards are in
+    the table and must not be dropped -> no retry."""
     while True:
         try:
-            engine.count(d_text, n, mask)
+            engine.pretokenize_count(d_text, n, cuts=cuts)
             return
         except _lib.BpeError as e:
             if e.code != _lib.ERR_CAPACITY or keep_counted or not engine.grow():
@@ -253,7 +257,7 @@ def _pretokenize_file(file_path, n_chunks: int, training, special_tokens, strict
     engine.set_special_tokens([])
     engine.unique_reset()
     d_text, n = engine.to_device(b"".join(pieces))
-    engine.count(d_text, n, engine.scan(d_text, n, cuts=cuts[:-1]))
+    count_with_growth(engine, d_text, n, cuts[:-1])
     return counter_from_engine(engine)
 
 

@@ -103,6 +103,15 @@ int bpe_scan(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint64_t* d_
  * (pretokenization.py:73-111, 171-208).  Special tokens are left out.  Callable once per shard / chunk. */
 int bpe_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, void* stream);
 
+/* bpe_scan + bpe_count in ONE pass over the text: pretokenize_chunk as a whole (pretokenization.py:171-208 — split on the
+ * special tokens, the split pattern, the Counter).  The token starts stay in registers; every pretoken is hashed and
+ * counted where it is found, so the text is read once and no start mask is written or read back.  Same segmentation
+ * arguments as bpe_scan; same table, same results as bpe_scan followed by bpe_count.  d_start may be NULL; if it is not,
+ * the start mask is written as well (n/32 + 2 words).  On BPE_ERR_INVALID_UTF8 the table may already hold counts of this
+ * text: the caller resets it (bpe_unique_reset) before counting the repaired bytes. */
+int bpe_pretokenize_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint64_t* d_cuts, uint64_t n_cuts,
+                          uint32_t flags, uint32_t* d_start, void* stream);
+
 /* Number of distinct pretokens counted so far, the sum of their lengths, and the total occurrences. */
 int bpe_unique_stats(bpe_ctx* ctx, uint64_t* n_unique, uint64_t* n_bytes, uint64_t* n_tokens);
 

@@ -33,15 +33,23 @@ def engine():
 
 
 def gpu_mask(engine, data: bytes, specials=None, cuts=None, flags=0) -> np.ndarray:
+    """The start mask from bpe_scan, checked against the one the fused one-pass kernel (bpe_pretokenize_count) writes:
+    two implementations of the same rule (a CTA per tile with shared memory there, a warp per window with shuffles here)."""
     from bpe_transformer_b200 import _lib
 
     engine.set_special_tokens(_lib.sort_specials(specials))
     d_text, n = engine.to_device(data)
     mask = engine.scan(d_text, n, cuts=cuts, flags=flags)
-    return mask.cpu().numpy().view(np.uint32)[:(n + 31) // 32]
+    out = mask.cpu().numpy().view(np.uint32)[:(n + 31) // 32]
+    if n:
+        engine.unique_reset()
+        fused = engine.pretokenize_count(d_text, n, cuts=cuts, flags=flags, want_mask=True).cpu().numpy().view(np.uint32)[:(n + 31) // 32]
+        assert np.array_equal(fused, out), "fused kernel's mask differs from bpe_scan's: " + first_diff(fused, out, data)
+    return out
 
 
 def gpu_counter(engine, data: bytes, specials=None, cuts=None, flags=0) -> Counter:
+    """The Counter from bpe_scan + bpe_count, checked against the one from the fused one-pass kernel."""
     from bpe_transformer_b200 import _lib
     from bpe_transformer_b200.tokenization.preprocessing.pretokenization import counter_from_engine
 
@@ -49,7 +57,17 @@ def gpu_counter(engine, data: bytes, specials=None, cuts=None, flags=0) -> Count
     engine.unique_reset()
     d_text, n = engine.to_device(data)
     engine.count(d_text, n, engine.scan(d_text, n, cuts=cuts, flags=flags))
-    return counter_from_engine(engine)
+    two_pass = counter_from_engine(engine)
+    stats = engine.unique_stats()
+    engine.unique_reset()
+    engine.pretokenize_count(d_text, n, cuts=cuts, flags=flags)
+    fused = counter_from_engine(engine)
+    if fused != two_pass:
+        only = [(bytes(k), v, two_pass.get(k)) for k, v in fused.items() if two_pass.get(k) != v][:5]
+        missing = [(bytes(k), v) for k, v in two_pass.items() if k not in fused][:5]
+        raise AssertionError(f"fused counter differs: fused-vs-two-pass {only}, missing from fused {missing}")
+    assert engine.unique_stats() == stats
+    return two_pass
 
 
 def first_diff(a: np.ndarray, b: np.ndarray, data: bytes) -> str:
@@ -176,6 +194,47 @@ def test_public_pretokenize_wrappers_match_reference_golden(case, input_bytes, t
 def test_counts_match_oracle_synthetic(engine, style, seed, size):
     data = synth_corpus(style, seed, size)
     assert gpu_counter(engine, data, [EOT]) == c_oracle.count(data, [EOT])
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+@pytest.mark.parametrize("specials", [[], [EOT], [EOT, EOT + EOT, "<|"]])
+def test_count_fuzz_matches_oracle(engine, seed, specials):
+    """The fuzz strings of the scan test as one text, counted: with cuts, as one piece, cut after newlines."""
+    rnd = random.Random(100 + seed)
+    pieces, cuts, total = [], [], 0
+    for _ in range(3000):
+        s = "".join(rnd.choice(ALPHABET) for _ in range(rnd.randint(1, 60))).encode("utf-8")
+        pieces.append(s)
+        total += len(s)
+        cuts.append(total)
+    data = b"".join(pieces)
+    assert gpu_counter(engine, data, specials, cuts[:-1]) == c_oracle.count(data, specials, cuts[:-1])
+    for flags in (0, c_oracle.CUT_AFTER_NEWLINE):
+        assert gpu_counter(engine, data, specials, None, flags) == c_oracle.count(data, specials, None, flags)
+
+
+def test_count_long_tokens_and_window_borders(engine):
+    """Pretokens far longer than a lane, a window, a CTA's range; special tokens, contractions and multi-byte characters on
+    window borders; every shift of the text against the 928-byte windows."""
+    parts = [b"a" * 20000, b" " * 9000, b"x", b"-" * 8190, EOT.encode(), b"'ll" * 3000, ("\u00e9" * 5000).encode(), b"\n" * 8193, b"7" * 100,
+             b" word" * 500, b"q" * 70000, b" tail", EOT.encode(), b"z" * 927, b" ", b"y" * 929, b"!" * 31, b"w" * 33]
+    data = b"".join(parts)
+    for shift in list(range(0, 40, 7)) + [900, 927, 928, 929]:
+        d = b"z" * shift + data
+        assert gpu_counter(engine, d, [EOT]) == c_oracle.count(d, [EOT])
+    huge = b"ab " + b"k" * 3_000_000 + b" cd " + b" " * 1_000_000 + b"e"
+    assert gpu_counter(engine, huge, [EOT]) == c_oracle.count(huge, [EOT])
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 63, 64, 65, 927, 928, 929, 960, 8191, 8192, 8193, 16 * 928, 16 * 928 + 1, 16384 + 5])
+def test_count_edge_sizes(engine, n):
+    data = synth_corpus(1, 78, 40000)[:n]
+    while data and (data[-1] & 0xC0) == 0x80:
+        data = data[:-1]
+    if data and data[-1] >= 0xC0:
+        data = data[:-1]
+    for specials in ([], [EOT]):
+        assert gpu_counter(engine, data, specials) == c_oracle.count(data, specials)
 
 
 def test_count_accumulates_over_shards(engine):
