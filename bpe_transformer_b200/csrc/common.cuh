@@ -54,35 +54,17 @@ struct Specials {
 };
 
 // ---- the 64-bit key of a byte string ------------------------------------------------------------------------------
-// Internal to the library (the oracle compares byte strings, never hashes).  The key is a finalised polynomial
-// hash: H(b_0 .. b_{L-1}) = sum b_j R^(L-1-j) mod 2^64, i.e. Horner's rule one byte at a time.  That form is what lets
-// the fused kernels (fused.cu) hash every token of a text in one sweep: a lane runs Horner over its own 32 bytes,
-// restarting at token starts, and a token that spans lanes is put together from the pieces as H_left * R^n + H_right.
-// Every path that names a pretoken by key (count, import, encode lookup) uses the same function.
-#define BPE_HASH_R 0x9E3779B1u  // odd, 32 bits: h * R + b is one wide multiply-add and one multiply-add
-
-__device__ __forceinline__ uint64_t poly_step(uint64_t h, uint32_t b) {
-    const uint64_t t = (uint64_t)(uint32_t)h * BPE_HASH_R + b;
-    return ((uint64_t)((uint32_t)(h >> 32) * BPE_HASH_R + (uint32_t)(t >> 32)) << 32) | (uint32_t)t;
+// Internal to the library (the oracle compares byte strings, never hashes).  Eight bytes per round; the same function
+// wherever a pretoken is named by key (count, import, encode lookup), whether its bytes come from global memory, from
+// a window of text staged in shared memory (fused.cu) or from a kernel parameter (the special tokens).
+__device__ __forceinline__ uint64_t mix64(uint64_t h, uint64_t w) {
+    h = (h ^ w) * 0x9FB21C651E98DF25ull;
+    return h ^ (h >> 35);
 }
-
-// h * R^k for the combination of pieces (k is small on the paths that call this: one step per byte).
-__device__ __forceinline__ uint64_t poly_shift(uint64_t h, uint64_t k) {
-    uint64_t r = BPE_HASH_R, acc = 1;
-    for (; k; k >>= 1) {
-        if (k & 1) acc *= r;
-        r *= r;
-    }
-    return h * acc;
-}
-
-// Never 0 (0 marks an empty slot).  A bijection of H + len * C apart from 0 -> 1.
-__device__ __forceinline__ uint64_t key_finalize(uint64_t h, uint64_t len) {
-    uint64_t k = h + len * 0x9E3779B97F4A7C15ull;
-    k ^= k >> 32;
-    k *= 0xD6E8FEB86659FD93ull;
-    k ^= k >> 29;
-    return k ? k : 1ull;
+__device__ __forceinline__ uint64_t key_seed(uint64_t len) { return 0x243F6A8885A308D3ull ^ (len * 0x9E3779B97F4A7C15ull); }
+__device__ __forceinline__ uint64_t key_finish(uint64_t h) {
+    h ^= h >> 29;
+    return h ? h : 1ull;  // never 0 (0 marks an empty slot)
 }
 
 // Unaligned little-endian 64-bit read through two aligned reads (the buffer is padded: BPE_TEXT_PAD).
@@ -99,6 +81,20 @@ struct TokenKey {
     uint64_t key;  // never 0
 };
 
+__device__ __forceinline__ uint64_t hash_key(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
+    uint64_t h = key_seed(len), o = 0;
+#pragma unroll 1
+    for (; o + 8 <= len; o += 8) h = mix64(h, load_u64_unaligned(base, p + o));
+    if (o < len) h = mix64(h, load_u64_unaligned(base, p + o) & ((1ull << ((len - o) * 8)) - 1ull));
+    return key_finish(h);
+}
+
+__device__ __forceinline__ TokenKey hash_bytes(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
+    TokenKey k;
+    k.key = hash_key(base, p, len);
+    return k;
+}
+
 // text[p, p + len) == special token s ?  Eight bytes per compare (the text buffer is padded, so the last word may be read whole).
 __device__ __forceinline__ bool special_equals(const Specials& sp, int s, const uint8_t* __restrict__ text, uint64_t p, uint32_t len) {
     bool ok = true;
@@ -109,31 +105,6 @@ __device__ __forceinline__ bool special_equals(const Specials& sp, int s, const 
         ok = w == sp.words[s][k];
     }
     return ok;
-}
-
-__device__ __forceinline__ uint64_t poly_hash(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
-    uint64_t h = 0, o = 0;
-#pragma unroll 1
-    for (; o + 8 <= len; o += 8) {
-        uint64_t w = load_u64_unaligned(base, p + o);
-#pragma unroll
-        for (int k = 0; k < 8; k++) h = poly_step(h, (uint32_t)(w >> (8 * k)) & 0xFFu);
-    }
-    if (o < len) {
-        uint64_t w = load_u64_unaligned(base, p + o);
-        for (uint64_t k = 0; k < len - o; k++) h = poly_step(h, (uint32_t)(w >> (8 * k)) & 0xFFu);
-    }
-    return h;
-}
-
-__device__ __forceinline__ TokenKey hash_bytes(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
-    TokenKey k;
-    k.key = key_finalize(poly_hash(base, p, len), len);
-    return k;
-}
-
-__device__ __forceinline__ uint64_t hash_key(const uint8_t* __restrict__ base, uint64_t p, uint32_t len) {
-    return key_finalize(poly_hash(base, p, len), len);
 }
 
 // ---- the table of distinct pretokens (context-owned, global memory) ---------------------------------------
