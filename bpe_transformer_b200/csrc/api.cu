@@ -103,6 +103,8 @@ int bpe_ctx_create(int device, bpe_ctx** out) {
     if (e != cudaSuccess) return ctx_fail(nullptr, BPE_ERR_CUDA, "cudaSetDevice", e);
     bpe_ctx* ctx = new bpe_ctx();
     ctx->device = device;
+    cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device);
+    if (ctx->n_sm <= 0) ctx->n_sm = BPE_N_SM;
     auto fail = [&](const char* what, cudaError_t err) { ctx_fail(nullptr, BPE_ERR_CUDA, what, err); bpe_ctx_destroy(ctx); return BPE_ERR_CUDA; };
     if ((e = cudaMalloc(&ctx->d_status, 4)) != cudaSuccess) return fail("cudaMalloc(status)", e);
     if ((e = cudaMemset(ctx->d_status, 0, 4)) != cudaSuccess) return fail("cudaMemset(status)", e);

@@ -127,12 +127,27 @@ struct UniqueTable {
 
 __device__ __forceinline__ void set_status(uint32_t* status, uint32_t bit) { atomicOr(status, bit); }
 
-// Do text[p, p + len) and the pool copy of `slot` hold the same bytes?  The caller has seen chk[slot] != 0.
+// Do text[p, p + len) and the pool copy of `slot` hold the same bytes?  The caller has seen chk[slot] != 0.  Eight bytes per
+// compare; the pool is read through L2 (another SM may have written it during this kernel), the text through the read-only path.
 __device__ __forceinline__ bool unique_same_bytes(const UniqueTable& t, uint64_t slot, const uint8_t* __restrict__ text, uint64_t p, uint64_t len) {
     if (*reinterpret_cast<volatile uint32_t*>(t.len + slot) != (uint32_t)len) return false;
-    const volatile uint8_t* q = t.pool + *reinterpret_cast<volatile uint64_t*>(t.pool_off + slot);
-    for (uint64_t i = 0; i < len; i++)
-        if (q[i] != text[p + i]) return false;
+    const uint64_t off = *reinterpret_cast<volatile uint64_t*>(t.pool_off + slot);
+    const uint64_t* q = reinterpret_cast<const uint64_t*>(t.pool) + (off >> 3);
+    const uint32_t sh = (uint32_t)(off & 7) * 8u;
+    uint64_t lo = __ldcg(q);
+#pragma unroll 1
+    for (uint64_t o = 0; o < len; o += 8) {
+        const uint64_t hi = __ldcg(q + (o >> 3) + 1);  // the pool is padded (BPE_TEXT_PAD)
+        uint64_t a = sh ? (lo >> sh) | (hi << (64u - sh)) : lo;
+        uint64_t b = load_u64_unaligned(text, p + o);
+        if (len - o < 8) {
+            const uint64_t keep = (1ull << ((len - o) * 8)) - 1ull;
+            a &= keep;
+            b &= keep;
+        }
+        if (a != b) return false;
+        lo = hi;
+    }
     return true;
 }
 
@@ -253,6 +268,7 @@ struct KernelTimer;
 
 struct bpe_ctx {
     int device = 0;
+    int n_sm = BPE_N_SM;  // multiprocessors of this device (cooperative grids are sized by it)
     std::string err;
     uint32_t* d_status = nullptr;  // status word
     ClassTables cls{};

@@ -150,7 +150,7 @@ __device__ __forceinline__ uint64_t hash_key_staged(const uint4* stage, uint32_t
 // The first token start at or behind byte `chunk` * 32 (or the end of the text): where a token that is still open at the end
 // of a window's right ghost lane ends.  Walks on window by window; warp-uniform; all lanes call.
 template <bool NLMODE>
-__device__ __noinline__ uint64_t find_token_end(const FusedParams& P, const Specials& sp, int64_t chunk) {
+__device__ __noinline__ uint64_t find_token_end(const PretokParams& P, const Specials& sp, int64_t chunk) {
     const uint32_t lane = threadIdx.x & 31;
     const SpecialFirst sf = special_first(sp);
     for (;;) {
@@ -371,6 +371,7 @@ __global__ void __launch_bounds__(FC_THREADS, 1) fused_count_kernel(const __grid
     }
     if (lane == 0 && tokens) atomicAdd(reinterpret_cast<unsigned long long*>(P.ut.counters + 2), (unsigned long long)tokens);
 }
+
 
 }  // namespace
 

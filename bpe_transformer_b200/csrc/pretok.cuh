@@ -145,11 +145,12 @@ struct ChunkClasses {
 // Two words (8 bytes) per trip and the eight words rotated by two after each trip — four trips put them back where they
 // were — so that the loop body exists once: the fused kernels' hot loop has to fit the instruction cache, and indexing
 // the register array with the trip count would push it to local memory.
-template <bool NLMODE>
+// (COMPACT = false unrolls the four trips: faster where the instruction cache is no concern, as in scan.cu's small kernel.)
+template <bool NLMODE, bool COMPACT = true>
 __device__ __forceinline__ ChunkClasses classify_chunk(const PretokParams& P, const Specials& sp, const SpecialFirst& sf, uint32_t (&w)[8],
                                                        uint64_t c0, uint32_t valid) {
     uint32_t L = 0, N = 0, S = 0, SP = 0, NL = 0, AP = 0, HI = 0, FB = 0;
-#pragma unroll 1
+#pragma unroll(COMPACT ? 1 : 4)
     for (int trip = 0; trip < 4; trip++) {
         uint32_t l8 = 0, n8 = 0, s8 = 0, sp8 = 0, nl8 = 0, ap8 = 0, hi8 = 0, fb8 = 0;
 #pragma unroll

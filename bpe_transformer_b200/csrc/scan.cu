@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const ScanParams P, 
             if (c0 + 16 < P.n) b = __ldg(q + 1);
             w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
         }
-        const ChunkClasses c = classify_chunk<NLMODE>(P, sp, sf, w, c0, valid);
+        const ChunkClasses c = classify_chunk<NLMODE, false>(P, sp, sf, w, c0, valid);
         e_hi[tid] = edge_hi(c);
         e_lo[tid] = edge_lo(c);
         fbm[tid] = c.FB;

@@ -410,6 +410,31 @@ def test_encode_matches_oracle_synthetic(model, style, seed, gpt2_model, ts10k_m
     assert tok.decode_array(got) == data
 
 
+def test_encode_with_a_caller_made_start_mask_equals_the_one_pass_path(engine, ts10k_model, tmp_path):
+    """bpe_encode takes an optional start mask made by bpe_scan: that path (mask kernel, count, emit over the mask) and the
+    one-pass path (no mask) must give the same ids, cold and warm."""
+    from adapters import get_tokenizer
+    from bpe_transformer_b200 import _lib
+
+    vocab, merges = ts10k_model
+    tok = get_tokenizer(with_specials(vocab, [EOT]), merges, [EOT])
+    data = synth_corpus(1, 53, 2_000_000) + ("tail without newline " + EOT + " x" * 700 + "q" * 5000).encode()
+    for flags in (0, _lib.CUT_AFTER_NEWLINE):
+        engine.unique_reset()
+        tok._bind(engine)
+        d_text, n = engine.to_device(data)
+        one_pass = [engine.encode(d_text, n, flags=flags).cpu().numpy().view(np.uint16) for _ in range(2)]
+        engine.unique_reset()
+        tok._device_model = None
+        engine._model_token = None
+        tok._bind(engine)
+        mask = engine.scan(d_text, n, flags=flags)
+        with_mask = [engine.encode(d_text, n, flags=flags, mask=mask).cpu().numpy().view(np.uint16) for _ in range(2)]
+        want = np.asarray(c_oracle.COracleTokenizer(tok.vocab, merges, [EOT]).encode_bytes(data, flags=flags), dtype=np.uint16)
+        for got in one_pass + with_mask:
+            assert np.array_equal(got, want)
+
+
 def test_encode_with_a_freshly_trained_vocab(tmp_path):
     """train on the GPU, encode with the result, check both against the port."""
     from adapters import get_tokenizer, run_train_bpe
