@@ -326,13 +326,17 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
 
     result = {}
 
-    def train_step_resident():
+    def train_step_resident(design=None):
+        design = design or args.merge_loop
         eng.unique_reset()
         eng.pretokenize_count(d_text, n_local)
         if world > 1:
             D.exchange_unique(eng)
         tr = BPETrainer(vocab_size=VOCAB_SIZE, special_tokens=specials)
-        tr._merge_tokens(eng)
+        if world > 1 and design == "shared":
+            D.merge_tokens_together(tr, eng)
+        else:
+            tr._merge_tokens(eng)
         result["trainer"] = tr
 
     for _ in range(args.warmup):
@@ -356,11 +360,31 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
     log(f"[bench] train resident: {step_ms:.1f} ms/step, {len(tr.merges)} merges, {n_unique} distinct pretokens, "
         f"merge loop {timing['merge_loop_ms']:.1f} ms / {timing['iterations']} iterations")
 
+    # ---- N > 1: the other design of the merge loop, measured the same way (DESIGN.md section 5 keeps both numbers) ----------
+    designs = None
+    if world > 1:
+        other = "shared" if args.merge_loop == "replicated" else "replicated"
+        train_step_resident(other)
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(2):
+            train_step_resident(other)
+        e1.record()
+        sync_all()
+        other_ms = max_over_ranks(e0.elapsed_time(e1) / 2)
+        tr_other = result["trainer"]
+        designs = {args.merge_loop: {"step_ms": step_ms, "merge_loop_ms": timing["merge_loop_ms"]},
+                   other: {"step_ms": other_ms, "merge_loop_ms": tr_other.last_timing["merge_loop_ms"]},
+                   "timed": args.merge_loop, "same_merges": tr_other.merges == tr.merges}
+        log(f"[bench] merge loop designs at N={world}: {args.merge_loop} {step_ms:.1f} ms/step (loop {timing['merge_loop_ms']:.1f}), "
+            f"{other} {other_ms:.1f} ms/step (loop {tr_other.last_timing['merge_loop_ms']:.1f}), same merges {designs['same_merges']}")
+
     # ---- end to end through the public API ---------------------------------------------------------------------
     def train_e2e():
         if world == 1:
             return train_bpe(path, VOCAB_SIZE, specials)
-        return D.train_bpe_sharded(path, VOCAB_SIZE, specials)
+        return D.train_bpe_sharded(path, VOCAB_SIZE, specials, merge_loop=args.merge_loop)
 
     train_e2e()
     sync_all()
@@ -493,6 +517,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
                            "api": "BPETokenizer.encode_file_to_array(path, out=<page-locked uint16 array, allocated once>) (= encode_iterable(open(path)) as an array)",
                            "fresh_pageable_array_per_call": total / enc_e2e_pageable_s / 1e9},
                    "ids": n_ids_total, "algorithmic_bytes": int(total + 2 * n_ids_total), "roundtrip_decode_equals_input": roundtrip_ok},
+        "merge_loop_designs": designs,
         "distinct_pretokens": int(n_unique), "pretokens": int(n_tokens), "merges": len(merges),
         "kernels": kernels, "clocks": clocks,
     }
@@ -572,6 +597,8 @@ def main():
     ap.add_argument("--bytes", type=int, default=int(os.environ.get("BPE_BENCH_BYTES", 2_100_000_000)))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample-bytes", type=int, default=64_000_000)
+    ap.add_argument("--merge-loop", default="replicated", choices=["replicated", "shared"],
+                    help="N > 1: the design of the merge loop that is timed (the other one is measured beside it)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline and the parity gate against it")
     ap.add_argument("--no-cpu-encode", action="store_true", help="--impl reference: skip the CPU encode timings")
     args = ap.parse_args()
@@ -583,6 +610,7 @@ def main():
         run_reference(args, rank, world)
         return
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG", "WARN")  # NCCL's version banner goes to stdout otherwise: stdout carries ONE JSON line
         import torch
         import torch.distributed as dist
 

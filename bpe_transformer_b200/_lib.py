@@ -27,6 +27,7 @@ SYMBOLS = [
     "bpe_count", "bpe_unique_stats", "bpe_unique_export", "bpe_unique_import", "bpe_unique_reset", "bpe_train",
     "bpe_train_timing", "bpe_load_model", "bpe_encode", "bpe_decode", "bpe_kernel_times", "bpe_set_profiling",
     "bpe_decode_noalloc", "bpe_load_file", "bpe_store_to_host", "bpe_load_file_ranges", "bpe_pretokenize_count",
+    "bpe_peer_alloc", "bpe_peer_connect", "bpe_peer_disconnect",
 ]
 
 
@@ -75,6 +76,9 @@ def load_library():
         lib.bpe_unique_reset.argtypes = [vp]
         lib.bpe_train.argtypes = [vp, C.c_uint32, C.c_uint32, u8p, u32p, u32p, u32p, C.POINTER(C.c_uint32), vp]
         lib.bpe_train_timing.argtypes = [vp, C.POINTER(C.c_double)]
+        lib.bpe_peer_alloc.argtypes = [vp, C.c_uint32, u8p]
+        lib.bpe_peer_connect.argtypes = [vp, C.c_int, C.c_int, u8p]
+        lib.bpe_peer_disconnect.argtypes = [vp]
         lib.bpe_load_model.argtypes = [vp, u32p, u32p, u32p, C.c_uint32, u32p, u32p]
         lib.bpe_encode.argtypes = [vp, u8p, C.c_uint64, u64p, C.c_uint64, C.c_uint32, u32p, vp, C.c_int, C.c_uint64,
                                    C.POINTER(C.c_uint64), vp]
@@ -300,6 +304,19 @@ class Engine:
         self._check(self.lib.bpe_train(self.ctx, vocab_size, first_new, _np_ptr(blob), _np_ptr(off), _np_ptr(ma), _np_ptr(mb),
                                        C.byref(nm), self._stream()))
         return ma[:nm.value], mb[:nm.value]
+
+    def peer_alloc(self, hits_per_sender: int) -> bytes:
+        """This GPU's exchange buffer for shared heavy steps; returns the 64-byte handle the peers open it with."""
+        h = np.zeros(64, dtype=np.uint8)
+        self._check(self.lib.bpe_peer_alloc(self.ctx, int(hits_per_sender), _np_ptr(h)))
+        return h.tobytes()
+
+    def peer_connect(self, rank: int, handles: list[bytes]):
+        blob = np.frombuffer(b"".join(handles), dtype=np.uint8).copy()
+        self._check(self.lib.bpe_peer_connect(self.ctx, int(rank), len(handles), _np_ptr(blob)))
+
+    def peer_disconnect(self):
+        self._check(self.lib.bpe_peer_disconnect(self.ctx))
 
     def train_timing(self) -> tuple[float, float, int]:
         out = (C.c_double * 3)()

@@ -10,6 +10,14 @@
 
 static std::string g_create_error;
 
+// Closes the peers' exchange buffers (bpe_peer_connect); this GPU's own buffer stays.
+static void peer_release(bpe_ctx* ctx) {
+    for (int p = 0; p < ctx->peer_world; p++)
+        if (ctx->peer_ptr[p] && ctx->peer_ptr[p] != ctx->peer_buf) cudaIpcCloseMemHandle(ctx->peer_ptr[p]);
+    for (auto& p : ctx->peer_ptr) p = nullptr;
+    ctx->peer_world = 1; ctx->peer_rank = 0; ctx->train_sharded = false;
+}
+
 int ctx_fail(bpe_ctx* ctx, int code, const char* what, cudaError_t e) {
     static std::mutex mu;  // bpe_load_file / bpe_store_to_host may run beside another call on the same context
     std::lock_guard<std::mutex> lock(mu);
@@ -128,6 +136,8 @@ void bpe_ctx_destroy(bpe_ctx* ctx) {
     cudaFree(ctx->d_idpool);
     for (auto& p : ctx->scratch) cudaFree(p);
     if (ctx->h_beat) cudaFreeHost(ctx->h_beat);
+    peer_release(ctx);
+    cudaFree(ctx->peer_buf);
     delete ctx;
 }
 
@@ -262,6 +272,52 @@ int bpe_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
     if (!ctx || !h_init_blob || !h_init_off || !n_merges || first_new_id < 256) return ctx ? ctx_fail(ctx, BPE_ERR_ARGUMENT, "bpe_train arguments") : BPE_ERR_ARGUMENT;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     return run_train(ctx, vocab_size, first_new_id, h_init_blob, h_init_off, h_merge_a, h_merge_b, n_merges, (cudaStream_t)stream);
+}
+
+int bpe_peer_alloc(bpe_ctx* ctx, uint32_t hits_per_sender, uint8_t h_handle[64]) {
+    if (!ctx || !h_handle || hits_per_sender == 0) return ctx ? ctx_fail(ctx, BPE_ERR_ARGUMENT, "bpe_peer_alloc arguments") : BPE_ERR_ARGUMENT;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    peer_release(ctx);
+    if (ctx->peer_buf) { cudaFree(ctx->peer_buf); ctx->peer_buf = nullptr; }
+    const size_t bytes = (2 * 8 + 2 * 8 * (size_t)hits_per_sender) * 8;  // flags + hit areas: 2 parities x 8 senders (train.cu: peer_flag / peer_entry)
+    CUDA_TRY(ctx, cudaMalloc(&ctx->peer_buf, bytes));
+    CUDA_TRY(ctx, cudaMemset(ctx->peer_buf, 0, bytes));
+    ctx->peer_cap = hits_per_sender;
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(ctx, cudaIpcGetMemHandle(&h, ctx->peer_buf));
+    memcpy(h_handle, &h, 64);
+    return BPE_OK;
+}
+
+int bpe_peer_connect(bpe_ctx* ctx, int rank, int world, const uint8_t* h_handles) {
+    if (!ctx || !h_handles || world < 2 || world > 8 || rank < 0 || rank >= world || !ctx->peer_buf)
+        return ctx ? ctx_fail(ctx, BPE_ERR_ARGUMENT, "bpe_peer_connect arguments (2..8 GPUs, after bpe_peer_alloc)") : BPE_ERR_ARGUMENT;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    peer_release(ctx);
+    for (int p = 0; p < world; p++) {
+        if (p == rank) { ctx->peer_ptr[p] = ctx->peer_buf; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, h_handles + 64 * p, 64);
+        cudaError_t e = cudaIpcOpenMemHandle(&ctx->peer_ptr[p], h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            ctx->peer_world = p;  // what has been opened so far
+            peer_release(ctx);
+            return ctx_fail(ctx, BPE_ERR_CUDA, "cudaIpcOpenMemHandle (peer exchange buffer)", e);
+        }
+    }
+    ctx->peer_rank = rank; ctx->peer_world = world; ctx->train_sharded = true;
+    return BPE_OK;
+}
+
+int bpe_peer_disconnect(bpe_ctx* ctx) {
+    if (!ctx) return BPE_ERR_ARGUMENT;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaDeviceSynchronize());
+    peer_release(ctx);
+    if (ctx->peer_buf) { cudaFree(ctx->peer_buf); ctx->peer_buf = nullptr; }
+    ctx->peer_cap = 0;
+    return BPE_OK;
 }
 
 int bpe_train_timing(bpe_ctx* ctx, double out[3]) {

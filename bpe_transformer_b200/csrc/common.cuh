@@ -298,6 +298,12 @@ struct bpe_ctx {
     void* scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     uint32_t* h_beat = nullptr;  // train.cu: pinned host words the merge loop writes its progress to
+    // sharded heavy steps (bpe_peer_*): this GPU's exchange buffer, the peers' buffers (opened through CUDA IPC), sizes
+    void* peer_buf = nullptr;
+    void* peer_ptr[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int peer_rank = 0, peer_world = 1;
+    uint32_t peer_cap = 0;
+    bool train_sharded = false;
     void* io_staging[2] = {nullptr, nullptr};  // io.cu: pinned staging buffers + copy streams; [0] loads, [1] stores (they may overlap)
     // timing
     bool profiling = false;

@@ -48,6 +48,9 @@ namespace cg = cooperative_groups;
 #define QUEUE_CAP 2048u
 #define NONE 0xFFFFFFFFu
 #define MAX_TIES 1024u            // pairs that tie at the top count and are ordered by their bytes
+#define W_MASK 0x1FFFFFFFu        // a posting's word index; the three bits above it name the GPU that filters the word in a sharded heavy step
+#define W_OWNER_SHIFT 29
+#define MAX_PEERS 8
 
 namespace {
 
@@ -58,9 +61,11 @@ struct Best {
 };
 
 struct Command {  // driver CTA -> helper CTAs, through global memory, ordered by the cluster / grid barrier
-    uint32_t op;  // 0 = exit, 1 = rewrite
+    uint32_t op;  // 0 = exit, 1 = rewrite (filter + rewrite; sharded: this GPU's share), 2 = sharded: rewrite the peers' hits
     uint32_t a, b, x, list_tok, list_len;
     long long threshold;
+    uint32_t heavy_id;  // number of the heavy step (its parity picks the exchange buffers)
+    uint32_t pad;
 };
 
 struct Ctrl {
@@ -73,6 +78,8 @@ struct Ctrl {
     unsigned int n_hot;       // length of `hot`
     unsigned int n_rebuilds;
     unsigned int n_heavy;
+    unsigned int out_n;       // sharded heavy step: hits this GPU has sent to its peers
+    unsigned int in_n[MAX_PEERS];  // ... and the hits each peer has sent here
     unsigned int go;          // grid variant: heavy steps announced by the driver CTA (helpers poll it)
     unsigned int done;        // grid variant: helper CTAs that finished their share, summed over all heavy steps
     unsigned int pad;
@@ -98,7 +105,25 @@ struct TrainState {
     uint32_t flags;  // bit 0: never use the shared-memory cache (experiments)
     uint32_t watchdog_s;
     volatile uint32_t* beat;  // pinned host memory: [2 * cta] = iteration, [2 * cta + 1] = phase (what the host prints if the loop stalls)
+    // ---- heavy steps shared between the GPUs of one box (csrc/train.cu header) ----
+    uint32_t rank, world;              // world == 1: everything below is unused
+    uint8_t* w_owner;                  // [n_words] the GPU that filters word w: a function of the pretoken's key, the same on every GPU
+    unsigned long long* w_key;         // [n_words] the pretoken's key: how a hit is named on the wire (word indices differ between GPUs)
+    uint32_t* slot_word;               // [table slots] word index of the pretoken in that slot of the context's table
+    const unsigned long long* ut_key;  // the context's table: key per slot
+    unsigned long long ut_mask;
+    unsigned long long* inbox[MAX_PEERS];  // inbox[p]: GPU p's exchange buffer (peer memory for p != rank).  Layout: see peer_entry / peer_flag
+    uint32_t inbox_cap;                // hits one sender may put into one receiver's buffer per heavy step
 };
+
+// Exchange buffer of one GPU: for each parity (heavy steps alternate) and each sender a flag word — (heavy step << 32) | hits —
+// followed by the senders' hit areas of inbox_cap keys each.
+__device__ __forceinline__ unsigned long long* peer_flag(const TrainState& S, uint32_t receiver, uint32_t parity, uint32_t sender) {
+    return S.inbox[receiver] + parity * MAX_PEERS + sender;
+}
+__device__ __forceinline__ unsigned long long* peer_entry(const TrainState& S, uint32_t receiver, uint32_t parity, uint32_t sender) {
+    return S.inbox[receiver] + 2 * MAX_PEERS + ((size_t)parity * MAX_PEERS + sender) * S.inbox_cap;
+}
 
 // Slot of pair `key` in the global table, inserted on first sight (compare-and-swap first: one round trip for a new pair).
 __device__ __forceinline__ uint64_t pair_slot(const TrainState& S, unsigned long long key) {
@@ -336,6 +361,12 @@ __global__ void words_build_kernel(UniqueTable ut, TrainState S) {
     unsigned int w = atomicAdd(&S.ctrl->n_words, 1u);
     unsigned int off = atomicAdd(&S.ctrl->sym_cursor, (len + 3u) & ~3u);  // 16-byte aligned: scanned with uint4 loads
     S.w_off[w] = off; S.w_len[w] = len; S.w_cnt[w] = (long long)ut.cnt[slot];
+    if (S.world > 1) {
+        const unsigned long long key = ut.key[slot];
+        S.w_key[w] = key;
+        S.w_owner[w] = (uint8_t)((key >> 40) % S.world);
+        S.slot_word[slot] = w;
+    }
     const uint8_t* src = ut.pool + ut.pool_off[slot];
     for (uint32_t k = 0; k < len; k++) S.sym[off + k] = src[k];
 }
@@ -407,7 +438,7 @@ __device__ __forceinline__ bool word_has_pair_loaded(const TrainState& S, uint32
 
 __device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, uint32_t off, uint32_t a, uint32_t b, uint32_t* len_out) {
     const uint4 v = __ldcg(reinterpret_cast<const uint4*>(S.sym + off));  // every word owns at least 4 symbol slots: load before the length is known
-    const uint32_t len = __ldcg(S.w_len + w);
+    const uint32_t len = __ldcg(S.w_len + (w & W_MASK));
     *len_out = len;
     return word_has_pair_loaded(S, off, v, len, a, b);
 }
@@ -416,6 +447,7 @@ __device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, u
 // Returns whether anything matched.  (Words longer than a warp, and queue overflow.)
 template <class Adder>
 __device__ bool rewrite_word_serial(const TrainState& S, uint32_t w, uint32_t off, uint32_t len, uint32_t a, uint32_t b, uint32_t x, const Adder& add) {
+    w &= W_MASK;
     uint32_t* s = S.sym + off;
     if (len < 2) return false;
     long long c = S.w_cnt[w];
@@ -453,10 +485,12 @@ __device__ bool rewrite_word_serial(const TrainState& S, uint32_t w, uint32_t of
 template <class Adder>
 __device__ bool rewrite_word_warp(const TrainState& S, uint32_t w, uint32_t off, uint32_t len, uint32_t a, uint32_t b, uint32_t x, const Adder& add) {
     const uint32_t lane = threadIdx.x & 31;
+    const uint32_t w_tagged = w;
+    w &= W_MASK;
     if (len == 0xFFFFu) len = __ldcg(S.w_len + w);  // the queue keeps 16 bits
     if (len < 2) return false;
     if (len > 32) {
-        bool hit = lane == 0 ? rewrite_word_serial(S, w, off, len, a, b, x, add) : false;
+        bool hit = lane == 0 ? rewrite_word_serial(S, w_tagged, off, len, a, b, x, add) : false;
         return __shfl_sync(0xFFFFFFFFu, hit, 0);
     }
     uint32_t* s = S.sym + off;
@@ -497,30 +531,46 @@ struct Queue {
     unsigned int n;
 };
 
+// Sharded heavy step: one more hit of this GPU's share goes to every peer, named by the pretoken's key.
+__device__ __forceinline__ void send_hit(const TrainState& S, uint32_t parity, uint32_t w) {
+    const unsigned long long key = S.w_key[w & W_MASK];
+    const unsigned int at = atomicAdd(&S.ctrl->out_n, 1u);
+    if (at >= S.inbox_cap) { set_status(S.status, ST_LIST_FULL); return; }
+    if (S.flags & 32u) return;  // experiments: no stores into peer memory
+    for (uint32_t p = 0; p < S.world; p++)
+        if (p != S.rank) peer_entry(S, p, parity, S.rank)[at] = key;  // a store into peer memory: over NVLink, no reply awaited
+}
+
 template <int NT>
 __device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t n_words, Queue& Q) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gsize = gridDim.x * NT;
     const uint2* list = cmd.list_tok == NONE ? nullptr : S.wl_pool + __ldcg(S.wl_off + cmd.list_tok);
     const uint32_t n_cand = list ? cmd.list_len : n_words;
     const GlobalAdder add{S, cmd.threshold};
+    const bool sharded = S.world > 1;  // every GPU filters the words it owns and tells the others what it found
+    const uint32_t parity = cmd.heavy_id & 1u;
     for (uint32_t base = blockIdx.x * NT; base < n_cand; base += gsize) {
         if (tid == 0) Q.n = 0;
         __syncthreads();
         const uint32_t i = base + tid;
         if (i < n_cand) {
             uint32_t w, off, len;
-            if (list) { const uint2 e = __ldcg(list + i); w = e.x; off = e.y; } else { w = i; off = S.w_off[i]; }
-            if (word_has_pair(S, w, off, cmd.a, cmd.b, &len)) {
+            if (list) { const uint2 e = __ldcg(list + i); w = e.x; off = e.y; }
+            else { w = sharded ? (i | ((uint32_t)S.w_owner[i] << W_OWNER_SHIFT)) : i; off = S.w_off[i]; }
+            if ((!sharded || (w >> W_OWNER_SHIFT) == S.rank) && word_has_pair(S, w, off, cmd.a, cmd.b, &len)) {
                 unsigned int q = atomicAdd(&Q.n, 1u);
                 if (q < QUEUE_CAP) { Q.w[q] = w; Q.off[q] = off; Q.len[q] = (unsigned short)min(len, 0xFFFFu); }
                 else if (rewrite_word_serial(S, w, off, len, cmd.a, cmd.b, cmd.x, add)) {
                     unsigned int at = atomicAdd(&S.ctrl->wl_cursor, 1u);
                     if (at < S.wl_cap) S.wl_pool[at] = make_uint2(w, off); else set_status(S.status, ST_LIST_FULL);
+                    if (sharded) send_hit(S, parity, w);
                 }
             }
         }
         __syncthreads();
         const uint32_t qn = min(Q.n, QUEUE_CAP);
+        if (sharded)
+            for (uint32_t k = tid; k < qn; k += NT) send_hit(S, parity, Q.w[k]);
         for (uint32_t k = warp; k < qn; k += NT / 32) {
             if (rewrite_word_warp(S, Q.w[k], Q.off[k], Q.len[k], cmd.a, cmd.b, cmd.x, add) && lane == 0) {
                 unsigned int at = atomicAdd(&S.ctrl->wl_cursor, 1u);
@@ -528,6 +578,42 @@ __device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t 
             }
         }
         __syncthreads();
+    }
+}
+
+// Second half of a sharded heavy step: the words the peers found in their shares, rewritten here as well (every GPU keeps
+// all words).  A hit arrives as the pretoken's key: key -> slot of the context's table -> this GPU's word index.
+template <int NT>
+__device__ void apply_remote_hits(const TrainState& S, const Command& cmd) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t gwarp = blockIdx.x * (NT / 32) + (threadIdx.x >> 5), n_warps = gridDim.x * (NT / 32);
+    const GlobalAdder add{S, cmd.threshold};
+    const uint32_t parity = cmd.heavy_id & 1u;
+    uint32_t base = 0;  // hits of the peers in front of p
+    for (uint32_t p = 0; p < S.world; p++) {
+        if (p == S.rank) continue;
+        const uint32_t n_p = __ldcg(&S.ctrl->in_n[p]);
+        const unsigned long long* hits = peer_entry(S, S.rank, parity, p);
+        // warps take hits round-robin over the concatenation of all peers' lists
+        for (uint32_t j = (gwarp + n_warps - base % n_warps) % n_warps; j < n_p; j += n_warps) {
+            const unsigned long long key = __ldcg(hits + j);
+            uint64_t slot = (key * 0xD6E8FEB86659FD93ull >> 17) & S.ut_mask;  // the slot sequence of unique_insert
+            uint32_t w = NONE;
+            for (uint32_t probe = 0; probe < 4096; probe++) {
+                const unsigned long long cur = __ldg(S.ut_key + slot);
+                if (cur == key) { w = __ldg(S.slot_word + slot); break; }
+                if (cur == 0) break;
+                slot = (slot + 1) & S.ut_mask;
+            }
+            if (w == NONE) { if (lane == 0) set_status(S.status, ST_LIST_FULL); continue; }  // cannot happen: every GPU holds the same pretokens
+            const uint32_t off = __ldcg(S.w_off + w);
+            const uint32_t tagged = w | (p << W_OWNER_SHIFT);
+            if (rewrite_word_warp(S, tagged, off, 0xFFFFu, cmd.a, cmd.b, cmd.x, add) && lane == 0) {
+                unsigned int at = atomicAdd(&S.ctrl->wl_cursor, 1u);
+                if (at < S.wl_cap) S.wl_pool[at] = make_uint2(tagged, off); else set_status(S.status, ST_LIST_FULL);
+            }
+        }
+        base += n_p;
     }
 }
 
@@ -552,7 +638,10 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
         if constexpr (CLUSTER) cg::this_cluster().sync();
         else {
             __syncthreads();
-            if (threadIdx.x == 0) { __threadfence(); atomicAdd(&S.ctrl->done, 1u); }
+            if (threadIdx.x == 0) {
+                if (S.world > 1) __threadfence_system(); else __threadfence();  // sharded: the CTA's stores into peer memory come first, for everyone
+                atomicAdd(&S.ctrl->done, 1u);
+            }
         }
     };
     auto driver_wake = [&] {  // the command has been written by thread 0
@@ -568,7 +657,10 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
             __syncthreads();
             if (threadIdx.x == 0) {
                 const unsigned int want = seen * (gridDim.x - 1);
-                while (*reinterpret_cast<volatile unsigned int*>(&S.ctrl->done) < want) {}
+                unsigned int spins_ = 0;
+                while (*reinterpret_cast<volatile unsigned int*>(&S.ctrl->done) < want) {
+                    if ((S.flags & 16u) && (++spins_ & 0xFFFFu) == 0) { S.beat[8000] = *reinterpret_cast<volatile unsigned int*>(&S.ctrl->done); S.beat[8001] = want; S.beat[8002] = seen; }
+                }
                 __threadfence();
             }
             __syncthreads();
@@ -600,18 +692,21 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
     if (blockIdx.x != 0) {  // helper CTAs: asleep on the barrier until the driver broadcasts a heavy step
         for (uint32_t round = 0;; round++) {
             if (tid == 0 && blockIdx.x < 16) { S.beat[2 * blockIdx.x] = round; S.beat[2 * blockIdx.x + 1] = 20; }
+            if (tid == 0 && (S.flags & 16u)) { S.beat[64 + 2 * blockIdx.x] = round; S.beat[64 + 2 * blockIdx.x + 1] = 20; }
             helper_wait();
             if (tid == 0) {
                 if (blockIdx.x < 16) S.beat[2 * blockIdx.x + 1] = 21;
                 const volatile Command* c = &S.ctrl->cmd;
                 sh_cmd.op = c->op; sh_cmd.a = c->a; sh_cmd.b = c->b; sh_cmd.x = c->x; sh_cmd.list_tok = c->list_tok;
-                sh_cmd.list_len = c->list_len; sh_cmd.threshold = c->threshold;
+                sh_cmd.list_len = c->list_len; sh_cmd.threshold = c->threshold; sh_cmd.heavy_id = c->heavy_id;
             }
             __syncthreads();
             const Command cmd = sh_cmd;
             if (cmd.op == 0) return;
-            heavy_rewrite<NT>(S, cmd, n_words, Q);
+            if (cmd.op == 2) apply_remote_hits<NT>(S, cmd);
+            else heavy_rewrite<NT>(S, cmd, n_words, Q);
             if (tid == 0 && blockIdx.x < 16) S.beat[2 * blockIdx.x + 1] = 22;
+            if (tid == 0 && (S.flags & 16u)) S.beat[64 + 2 * blockIdx.x + 1] = 22;
             helper_done();
         }
     }
@@ -922,7 +1017,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
                 for (int r = 0; r < 4; r++)
                     if (i0 + r * NT < list_len) {
                         v[r] = __ldcg(reinterpret_cast<const uint4*>(S.sym + e[r].y));
-                        len[r] = __ldcg(S.w_len + e[r].x);
+                        len[r] = __ldcg(S.w_len + (e[r].x & W_MASK));
                     }
 #pragma unroll
                 for (int r = 0; r < 4; r++)
@@ -1008,17 +1103,65 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
             if (tid == 0) {
                 S.ctrl->wl_cursor = wl_start;
                 S.ctrl->n_hot = 0;
-                S.ctrl->cmd = Command{1u, a, b, x, list_tok, list_len, T};
+                S.ctrl->out_n = 0;
+                S.ctrl->cmd = Command{1u, a, b, x, list_tok, list_len, T, n_heavy, 0u};
                 __threadfence();
                 if (beats) S.beat[1] = 7;
             }
             driver_wake();
             if (beats && tid == 0) S.beat[1] = 8;
             if (tracer) c3 = clock64();
-            const Command cmd{1u, a, b, x, list_tok, list_len, T};
+            const Command cmd{1u, a, b, x, list_tok, list_len, T, n_heavy, 0u};
             heavy_rewrite<NT>(S, cmd, n_words, Q);
             if (beats && tid == 0) S.beat[1] = 9;
             driver_join();
+            if (S.world > 1) {
+                // ---- the exchange: every GPU has filtered and rewritten its share and put the keys of its hits into the peers'
+                // buffers; now the counts go out (behind the hits: system-wide fence), the peers' counts come in, and the
+                // peers' hits are rewritten here too.  Same step on every GPU: they all run the same loop on the same data.
+                const uint32_t parity = n_heavy & 1u;
+                if (tid == 0) {
+                    __threadfence_system();
+                    const unsigned long long flag = ((unsigned long long)(n_heavy + 1u) << 32) | __ldcg(&S.ctrl->out_n);
+                    for (uint32_t p = 0; p < S.world; p++)
+                        if (p != S.rank) *reinterpret_cast<volatile unsigned long long*>(peer_flag(S, p, parity, S.rank)) = flag;
+                    __threadfence_system();
+                    S.beat[0] = iter; S.beat[1] = 30;
+                    unsigned long long t_wait0;
+                    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_wait0));
+                    for (uint32_t p = 0; p < S.world; p++) {
+                        if (p == S.rank) { S.ctrl->in_n[p] = 0; continue; }
+                        unsigned long long v;
+                        uint32_t polls = 0;
+                        for (;;) {
+                            v = *reinterpret_cast<volatile unsigned long long*>(peer_flag(S, S.rank, parity, p));
+                            if ((uint32_t)(v >> 32) == n_heavy + 1u) break;
+                            if ((++polls & 1023u) == 0) {  // a peer that never arrives must not hang this GPU for ever
+                                unsigned long long now;
+                                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                                if (now - t_wait0 > (unsigned long long)S.watchdog_s * 1000000000ull) {
+                                    set_status(S.status, ST_WATCHDOG);
+                                    S.ctrl->dbg[4] = iter; S.ctrl->dbg[5] = 0x1000u + p; S.ctrl->dbg[0] = (uint32_t)(v >> 32); S.ctrl->dbg[1] = (uint32_t)v;
+                                    v = 0;
+                                    break;
+                                }
+                            }
+                        }
+                        S.ctrl->in_n[p] = (uint32_t)v;
+                    }
+                    __threadfence_system();
+                    S.beat[1] = 31;
+                    S.ctrl->cmd = Command{2u, a, b, x, list_tok, list_len, T, n_heavy, 0u};
+                    __threadfence();
+                }
+                __syncthreads();  // the rest of this CTA reads the peers' counts too
+                driver_wake();
+                const Command cmd2{2u, a, b, x, list_tok, list_len, T, n_heavy, 0u};
+                apply_remote_hits<NT>(S, cmd2);
+                if (tid == 0) S.beat[1] = 32;
+                driver_join();
+                if (tid == 0) S.beat[1] = 33;
+            }
             if (beats && tid == 0) S.beat[1] = 10;
             matched = __ldcg(&S.ctrl->wl_cursor) - wl_start;
             for (uint32_t i = tid; i < n_cached; i += NT)
@@ -1113,7 +1256,7 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
     CUDA_TRY(ctx, cudaMemcpyAsync(h_counters, ctx->ut.counters, sizeof(h_counters), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(ctx, cudaStreamSynchronize(s));
     const uint64_t n_unique = h_counters[1], n_sym = h_counters[0];
-    if (n_unique == 0 || n_sym + 4 * n_unique >= 0xFFFFFFF0ull) return ctx_fail(ctx, n_unique ? BPE_ERR_CAPACITY : BPE_ERR_NO_PAIRS, "word table size");
+    if (n_unique == 0 || n_sym + 4 * n_unique >= 0xFFFFFFF0ull || n_unique > W_MASK) return ctx_fail(ctx, n_unique ? BPE_ERR_CAPACITY : BPE_ERR_NO_PAIRS, "word table size");
     if (vocab_size < first_new_id) vocab_size = first_new_id;  // nothing to learn, but "no pairs" is still an error
 
     cudaEvent_t ev[3];
@@ -1122,6 +1265,17 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
 
     TrainState S{};
     S.first_new_id = first_new_id; S.vocab_size = vocab_size; S.status = ctx->d_status;
+    // heavy steps shared with the other GPUs of the box, if the caller has connected them (bpe_peer_connect) and asked for it
+    const bool sharded = ctx->peer_world > 1 && ctx->train_sharded;
+    S.rank = sharded ? (uint32_t)ctx->peer_rank : 0u;
+    S.world = sharded ? (uint32_t)ctx->peer_world : 1u;
+    if (sharded) {
+        for (int p = 0; p < ctx->peer_world; p++) S.inbox[p] = (unsigned long long*)ctx->peer_ptr[p];
+        S.inbox_cap = ctx->peer_cap;
+        S.ut_key = (const unsigned long long*)ctx->ut.key;
+        S.ut_mask = ctx->ut.cap_mask;
+        if (n_unique / ctx->peer_world * 2 + 4096 > ctx->peer_cap) return ctx_fail(ctx, BPE_ERR_CAPACITY, "peer exchange buffers too small for this table (bpe_peer_alloc)");
+    }
     const size_t ph_cap = next_pow2(std::max<size_t>(1u << 16, 2 * n_sym));
     S.ph_mask = ph_cap - 1;
     const uint32_t init_bytes = h_init_off[first_new_id];
@@ -1137,6 +1291,8 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
         {(void**)&S.wl_off, (vocab_size + 1) * 4ull}, {(void**)&S.wl_len, (vocab_size + 1) * 4ull}, {(void**)&S.wl_pool, (size_t)S.wl_cap * 8},
         {(void**)&S.m_a, (vocab_size + 1) * 4ull}, {(void**)&S.m_b, (vocab_size + 1) * 4ull},
         {(void**)&S.ctrl, sizeof(Ctrl)}, {(void**)&S.trace, (vocab_size + 1) * 16ull},
+        {(void**)&S.w_owner, sharded ? n_unique : 0}, {(void**)&S.w_key, sharded ? n_unique * 8 : 0},
+        {(void**)&S.slot_word, sharded ? (ctx->ut.cap_mask + 1) * 4 : 0},
     };
     size_t total = 0;
     for (auto& p : parts) total += (p.bytes + 255) / 256 * 256;
@@ -1202,7 +1358,7 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
     // heavy steps get all SMs).  BPE_B200_TRAIN_MODE=cluster selects the single-cluster variant (experiments, tests).
     bool launched = false;
     const char* mode = getenv("BPE_B200_TRAIN_MODE");
-    if (mode && !strcmp(mode, "cluster")) {
+    if (mode && !strcmp(mode, "cluster") && !sharded) {
         auto kern = merge_loop_kernel<true, 1024>;
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DriverShared));
@@ -1247,9 +1403,15 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
         while (cudaEventQuery(done) == cudaErrorNotReady) {
             double waited = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
             if (waited > S.watchdog_s + 10.0) {
-                fprintf(stderr, "[bpe_train] merge loop stalled: driver at iteration %u phase %u;", h_beat[0], h_beat[1]);
+                fprintf(stderr, "[bpe_train rank %s] merge loop stalled: driver at iteration %u phase %u;", getenv("RANK") ? getenv("RANK") : "-", h_beat[0], h_beat[1]);
                 for (int c = 1; c < launched_ctas && c < 16; c++) fprintf(stderr, " cta%d round %u phase %u;", c, h_beat[2 * c], h_beat[2 * c + 1]);
                 fprintf(stderr, "\n");
+                if (S.flags & 16u) {
+                    fprintf(stderr, "[bpe_train] driver sees done %u of %u (hand-overs %u); helper CTAs not waiting for hand-over %u:", h_beat[8000], h_beat[8001], h_beat[8002], h_beat[8002]);
+                    for (int c = 1; c < launched_ctas; c++)
+                        if (h_beat[64 + 2 * c] != h_beat[8002] || h_beat[64 + 2 * c + 1] != 20) fprintf(stderr, " cta%d round %u phase %u;", c, h_beat[64 + 2 * c], h_beat[64 + 2 * c + 1]);
+                    fprintf(stderr, "\n");
+                }
                 cudaEventDestroy(done);
                 return ctx_fail(ctx, BPE_ERR_CUDA, "merge loop stalled (internal error); the process must exit");
             }

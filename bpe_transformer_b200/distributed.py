@@ -191,8 +191,31 @@ def count_shard(engine: "_lib.Engine", path, lo: int, hi: int, special_tokens: l
         pt.count_with_growth(engine, d_text, n, keep_counted=not reset)
 
 
-def train_bpe_sharded(input_path, vocab_size: int, special_tokens: list[str], group=None):
-    """train_bpe over the ranks of `group`: same (vocab, merges) on every rank, identical to one GPU's."""
+def merge_tokens_together(trainer, engine: "_lib.Engine", group=None) -> None:
+    """The merge loop with its heavy steps shared between the ranks' GPUs (one box, NVLink): every rank holds all
+    pretokens already (exchange_unique); exchange buffers are set up, every rank runs the same loop, and in a step with
+    a long candidate list each GPU filters only the words it owns and stores the keys of its hits into its peers' memory."""
+    import torch.distributed as dist
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    n_unique = engine.unique_stats()[0]
+    handle = engine.peer_alloc(2 * n_unique // world + 4096)
+    handles: list = [None] * world
+    dist.all_gather_object(handles, handle, group=group)
+    engine.peer_connect(rank, handles)
+    try:
+        dist.barrier(group=group)  # every buffer is open everywhere before the first kernel stores into a peer
+        trainer._merge_tokens(engine)
+    finally:
+        dist.barrier(group=group)  # nobody frees a buffer a peer may still be writing to
+        engine.peer_disconnect()
+
+
+def train_bpe_sharded(input_path, vocab_size: int, special_tokens: list[str], group=None, merge_loop: str = "replicated"):
+    """train_bpe over the ranks of `group`: same (vocab, merges) on every rank, identical to one GPU's.
+    merge_loop: "replicated" — every GPU runs the whole loop on its own (fastest while the table of distinct pretokens
+    is small: a TinyStories-sized one); "shared" — heavy steps are split between the GPUs over NVLink (wins when the table
+    is large: an OpenWebText-sized one).  DESIGN.md section 5 has both measured."""
     import torch.distributed as dist
 
     from .tokenization.bpe_trainer import BPETrainer
@@ -211,7 +234,12 @@ def train_bpe_sharded(input_path, vocab_size: int, special_tokens: list[str], gr
         order = [list(trainer.special_tokens)]
         dist.broadcast_object_list(order, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
         trainer.set_special_token_order(order[0])
-    trainer._merge_tokens(engine)
+    if merge_loop == "shared" and world > 1:
+        merge_tokens_together(trainer, engine, group)
+    elif merge_loop in ("replicated", "shared"):
+        trainer._merge_tokens(engine)
+    else:
+        raise ValueError('merge_loop must be "replicated" or "shared"')
     return trainer.vocab, trainer.merges
 
 

@@ -142,6 +142,19 @@ int bpe_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const ui
               const uint32_t* h_init_off, uint32_t* h_merge_a, uint32_t* h_merge_b, uint32_t* n_merges,
               void* stream);
 
+/* ---- training on several GPUs of one box: heavy steps of the merge loop shared over NVLink --------------------------
+ * (No counterpart in the reference, whose merge loop is one process: bpe_trainer.py:242-325.  BASELINE.json configs[2].)
+ * Every GPU holds all pretokens (after the table exchange) and runs the same loop; in a step whose candidate list is long,
+ * each GPU filters only the words it owns (a function of the pretoken's key), rewrites what it finds, and stores the keys of
+ * its hits straight into the other GPUs' exchange buffers (peer memory); then all rewrite the others' hits too.  Results are
+ * those of one GPU.  Set-up: every process calls bpe_peer_alloc (room for `hits_per_sender` hits per sender and step: at
+ * least 2 * distinct pretokens / GPUs + 4096), the 64-byte handles are exchanged by the host (an all-gather), every process
+ * calls bpe_peer_connect with all handles in rank order; bpe_train then shares its heavy steps.  All processes must call
+ * bpe_train together.  bpe_peer_disconnect (after a host barrier) returns to the single-GPU loop and frees the buffer. */
+int bpe_peer_alloc(bpe_ctx* ctx, uint32_t hits_per_sender, uint8_t h_handle[64]);
+int bpe_peer_connect(bpe_ctx* ctx, int rank, int world, const uint8_t* h_handles /* world x 64 bytes */);
+int bpe_peer_disconnect(bpe_ctx* ctx);
+
 /* Timing of the last bpe_train() on this context, in milliseconds of device time:
  * out[0] word table + pair histogram, out[1] merge loop, out[2] number of loop iterations. */
 int bpe_train_timing(bpe_ctx* ctx, double out[3]);
