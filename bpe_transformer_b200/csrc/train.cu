@@ -87,6 +87,7 @@ struct Ctrl {
     unsigned int dbg[8];      // flags bit 1: [0] stale cache copies, [1] first iteration with one, [2] hot pairs missing from the cache, [3] first iteration
     unsigned long long phase_clk[8];  // developer trace: SM cycles of the driver's thread 0 per phase, summed over iterations
     unsigned long long sub_clk[8];    // developer trace: inside the argmax (scan, barrier, ties, barrier, order + barrier)
+    unsigned long long heavy_clk[6];  // developer trace, heavy steps: drain, wake, own share, join, reload, rest
 };
 
 struct TrainState {
@@ -1099,7 +1100,10 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
             }
         } else {
             // heavy step: wake the helper CTAs; counts change behind the cache's back, so reload it afterwards
+            long long h0 = 0, h1 = 0, h2 = 0, h3 = 0, h4 = 0;
+            if (tracer) h0 = clock64();
             deferred_drain<NT>(S, H, DQ);  // queued updates land (and new cache entries learn their slots) before anyone reads global counts
+            if (tracer) h1 = clock64();
             if (tid == 0) {
                 S.ctrl->wl_cursor = wl_start;
                 S.ctrl->n_hot = 0;
@@ -1110,11 +1114,13 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
             }
             driver_wake();
             if (beats && tid == 0) S.beat[1] = 8;
-            if (tracer) c3 = clock64();
+            if (tracer) { c3 = clock64(); h2 = c3; }
             const Command cmd{1u, a, b, x, list_tok, list_len, T, n_heavy, 0u};
             heavy_rewrite<NT>(S, cmd, n_words, Q);
+            if (tracer) h3 = clock64();
             if (beats && tid == 0) S.beat[1] = 9;
             driver_join();
+            if (tracer) h4 = clock64();
             if (S.world > 1) {
                 // ---- the exchange: every GPU has filtered and rewritten its share and put the keys of its hits into the peers'
                 // buffers; now the counts go out (behind the hits: system-wide fence), the peers' counts come in, and the
@@ -1126,7 +1132,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
                     for (uint32_t p = 0; p < S.world; p++)
                         if (p != S.rank) *reinterpret_cast<volatile unsigned long long*>(peer_flag(S, p, parity, S.rank)) = flag;
                     __threadfence_system();
-                    S.beat[0] = iter; S.beat[1] = 30;
+                    if (beats) { S.beat[0] = iter; S.beat[1] = 30; }
                     unsigned long long t_wait0;
                     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_wait0));
                     for (uint32_t p = 0; p < S.world; p++) {
@@ -1150,7 +1156,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
                         S.ctrl->in_n[p] = (uint32_t)v;
                     }
                     __threadfence_system();
-                    S.beat[1] = 31;
+                    if (beats) S.beat[1] = 31;
                     S.ctrl->cmd = Command{2u, a, b, x, list_tok, list_len, T, n_heavy, 0u};
                     __threadfence();
                 }
@@ -1158,9 +1164,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
                 driver_wake();
                 const Command cmd2{2u, a, b, x, list_tok, list_len, T, n_heavy, 0u};
                 apply_remote_hits<NT>(S, cmd2);
-                if (tid == 0) S.beat[1] = 32;
                 driver_join();
-                if (tid == 0) S.beat[1] = 33;
             }
             if (beats && tid == 0) S.beat[1] = 10;
             matched = __ldcg(&S.ctrl->wl_cursor) - wl_start;
@@ -1174,6 +1178,11 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
                     hc_append(H, rec.x, (uint32_t)rec.y, __ldcg(S.ph_cnt + (uint32_t)rec.y), __ldcg(S.tk_pre + (uint32_t)((rec.x - 1) >> 32)));
             }
             n_heavy++;
+            if (tracer) {
+                const long long h5 = clock64();
+                S.ctrl->heavy_clk[0] += h1 - h0; S.ctrl->heavy_clk[1] += h2 - h1; S.ctrl->heavy_clk[2] += h3 - h2; S.ctrl->heavy_clk[3] += h4 - h3;
+                S.ctrl->heavy_clk[4] += h5 - h4; S.ctrl->heavy_clk[5] += h0 - c0;
+            }
         }
         if (tracer) c4 = clock64();
         // ---- close the step ---------------------------------------------------------------------------------------------
@@ -1439,6 +1448,8 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
         fprintf(stderr, "[train trace] driver thread 0, SM cycles per LIGHT step (%llu steps): argmax %.0f, select+bookkeeping %.0f, filter %.0f, rewrite %.0f, "
                         "close %.0f; per HEAVY step (%llu steps): %.0f; rebuilds %u\n", h_ctrl.phase_clk[6], h_ctrl.phase_clk[0] / nl, h_ctrl.phase_clk[1] / nl,
                 h_ctrl.phase_clk[2] / nl, h_ctrl.phase_clk[3] / nl, h_ctrl.phase_clk[4] / nl, h_ctrl.phase_clk[7], h_ctrl.phase_clk[5] / nh, h_ctrl.n_rebuilds);
+        fprintf(stderr, "[train trace] HEAVY step, cycles: argmax+select %.0f, drain %.0f, wake %.0f, own share %.0f, join %.0f, reload+pending %.0f\n",
+                h_ctrl.heavy_clk[5] / nh, h_ctrl.heavy_clk[0] / nh, h_ctrl.heavy_clk[1] / nh, h_ctrl.heavy_clk[2] / nh, h_ctrl.heavy_clk[3] / nh, h_ctrl.heavy_clk[4] / nh);
         const double ni = (double)std::max(1u, h_ctrl.n_iters);
         fprintf(stderr, "[train trace] argmax, cycles per step: scan %.0f, reduce+barrier %.0f, ties %.0f, barrier %.0f, order %.0f (candidates %.2f); entries scanned %.0f\n",
                 h_ctrl.sub_clk[0] / ni, h_ctrl.sub_clk[1] / ni, h_ctrl.sub_clk[2] / ni, h_ctrl.sub_clk[3] / ni, h_ctrl.sub_clk[4] / ni,

@@ -321,6 +321,33 @@ def test_train_matches_c_oracle_on_larger_corpora(style, seed, size, vocab_size,
     assert (vocab, merges) == (want_vocab, want_merges)
 
 
+def test_train_and_encode_owt_shaped_32k_vocab_golden(tmp_path):
+    """BASELINE configs[4] at a size a CPU finishes: OpenWebText-shaped text (128 MB, 8*10^5 distinct pretokens), vocab_size
+    32000.  Ordered merges and line-by-line ids against hashes made by oracle/gen_c5_golden.py (the port of the reference's
+    algorithm, pinned to the reference by tests/test_oracle_pinned.py; ids by the C oracle)."""
+    import hashlib
+
+    from adapters import get_tokenizer, run_train_bpe
+
+    g = load_golden("c5_owt_sha256.json.gz")
+    path = synth_corpus(g["style"], g["seed"], g["bytes"], str(tmp_path / "owt.txt"))
+    data = open(path, "rb").read()
+    assert len(data) == g["len"] and hashlib.sha256(data).hexdigest() == g["corpus_sha256"], "synthetic generator is not reproducible"
+    vocab, merges = run_train_bpe(path, g["vocab_size"], g["specials"])
+    assert len(merges) == g["merges"]
+    assert [[a.hex(), b.hex()] for a, b in merges[-5:]] == g["last_merges"]
+    h = hashlib.sha256()
+    for a, b in merges:
+        h.update(a.hex().encode() + b" " + b.hex().encode() + b"\n")
+    assert h.hexdigest() == g["merges_sha256"]
+    assert vocab[256] == EOT.encode() and all(vocab[257 + k] == a + b for k, (a, b) in enumerate(merges))
+    tok = get_tokenizer(vocab, merges, g["specials"])
+    ids = tok.encode_file_to_array(path)
+    assert ids.dtype == np.uint16 and len(ids) == g["ids"]
+    assert hashlib.sha256(ids.tobytes()).hexdigest() == g["ids_sha256"]
+    assert tok.decode_array(ids) == data
+
+
 def test_train_ignores_invalid_utf8_like_the_reference(tmp_file):
     """pretokenization.py:194 decodes with errors="ignore"."""
     from adapters import run_train_bpe
