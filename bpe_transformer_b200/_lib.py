@@ -27,7 +27,7 @@ SYMBOLS = [
     "bpe_count", "bpe_unique_stats", "bpe_unique_export", "bpe_unique_import", "bpe_unique_reset", "bpe_train",
     "bpe_train_timing", "bpe_load_model", "bpe_encode", "bpe_decode", "bpe_kernel_times", "bpe_set_profiling",
     "bpe_decode_noalloc", "bpe_load_file", "bpe_store_to_host", "bpe_load_file_ranges", "bpe_pretokenize_count",
-    "bpe_peer_alloc", "bpe_peer_connect", "bpe_peer_disconnect",
+    "bpe_peer_alloc", "bpe_peer_connect", "bpe_peer_disconnect", "bpe_debug_key_mask",
 ]
 
 
@@ -79,6 +79,7 @@ def load_library():
         lib.bpe_peer_alloc.argtypes = [vp, C.c_uint32, u8p]
         lib.bpe_peer_connect.argtypes = [vp, C.c_int, C.c_int, u8p]
         lib.bpe_peer_disconnect.argtypes = [vp]
+        lib.bpe_debug_key_mask.argtypes = [vp, C.c_uint64]
         lib.bpe_load_model.argtypes = [vp, u32p, u32p, u32p, C.c_uint32, u32p, u32p]
         lib.bpe_encode.argtypes = [vp, u8p, C.c_uint64, u64p, C.c_uint64, C.c_uint32, u32p, vp, C.c_int, C.c_uint64,
                                    C.POINTER(C.c_uint64), vp]
@@ -304,6 +305,10 @@ class Engine:
         self._check(self.lib.bpe_train(self.ctx, vocab_size, first_new, _np_ptr(blob), _np_ptr(off), _np_ptr(ma), _np_ptr(mb),
                                        C.byref(nm), self._stream()))
         return ma[:nm.value], mb[:nm.value]
+
+    def debug_key_mask(self, mask: int):
+        """Test hook: AND every pretoken key with `mask` (0xFFFF_FFFF_FFFF_FFFF = normal)."""
+        self._check(self.lib.bpe_debug_key_mask(self.ctx, int(mask)))
 
     def peer_alloc(self, hits_per_sender: int) -> bytes:
         """This GPU's exchange buffer for shared heavy steps; returns the 64-byte handle the peers open it with."""

@@ -399,6 +399,16 @@ int bpe_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_id
     return run_decode(ctx, d_ids, id_elem_bytes, n_ids, h_vocab_blob, h_vocab_off, n_vocab, d_bytes, cap, n_bytes, (cudaStream_t)stream);
 }
 
+int bpe_debug_key_mask(bpe_ctx* ctx, uint64_t mask) {
+    if (!ctx) return BPE_ERR_ARGUMENT;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaDeviceSynchronize());
+    CUDA_TRY(ctx, set_key_mask_count(mask));
+    CUDA_TRY(ctx, set_key_mask_fused(mask));
+    CUDA_TRY(ctx, set_key_mask_encode(mask));
+    return BPE_OK;
+}
+
 int bpe_kernel_times(bpe_ctx* ctx, bpe_kernel_time* out, int max) {
     if (!ctx) return 0;
     int n = 0;

@@ -62,8 +62,14 @@ __device__ __forceinline__ uint64_t mix64(uint64_t h, uint64_t w) {
     return h ^ (h >> 35);
 }
 __device__ __forceinline__ uint64_t key_seed(uint64_t len) { return 0x243F6A8885A308D3ull ^ (len * 0x9E3779B97F4A7C15ull); }
+// Test hook (bpe_debug_key_mask): keys are ANDed with this, so that a test can make distinct pretokens share a key and see
+// that the library reports it (BPE_ERR_HASH_COLLISION) instead of merging their counts.  All ones in normal operation.
+// One copy per translation unit (no relocatable device code): every .cu that hashes has a setter, api.cu calls them all.
+static __constant__ unsigned long long c_key_and = ~0ull;
+
 __device__ __forceinline__ uint64_t key_finish(uint64_t h) {
     h ^= h >> 29;
+    h &= c_key_and;
     return h ? h : 1ull;  // never 0 (0 marks an empty slot)
 }
 
@@ -352,6 +358,9 @@ struct KernelTimer {
 };
 
 void io_staging_free(bpe_ctx* ctx);
+cudaError_t set_key_mask_count(unsigned long long mask);   // count.cu
+cudaError_t set_key_mask_fused(unsigned long long mask);   // fused.cu
+cudaError_t set_key_mask_encode(unsigned long long mask);  // encode.cu
 
 // kernels launched from api.cu, defined in the other translation units
 int launch_scan(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_cutmask, uint32_t flags, uint32_t* d_start, cudaStream_t s);

@@ -218,3 +218,5 @@ int launch_export(bpe_ctx* ctx, uint8_t* d_blob, uint64_t* d_off, uint32_t* d_le
     CUDA_TRY(ctx, cudaGetLastError());
     return BPE_OK;
 }
+
+cudaError_t set_key_mask_count(unsigned long long mask) { return cudaMemcpyToSymbol(c_key_and, &mask, sizeof(mask)); }

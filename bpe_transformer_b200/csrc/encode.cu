@@ -605,3 +605,5 @@ extern "C" int bpe_decode_noalloc(const void* d_ids, int id_elem_bytes, uint64_t
     }
     return BPE_OK;
 }
+
+cudaError_t set_key_mask_encode(unsigned long long mask) { return cudaMemcpyToSymbol(c_key_and, &mask, sizeof(mask)); }

@@ -401,3 +401,5 @@ int launch_fused_count(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const ui
     CUDA_TRY(ctx, cudaGetLastError());
     return BPE_OK;
 }
+
+cudaError_t set_key_mask_fused(unsigned long long mask) { return cudaMemcpyToSymbol(c_key_and, &mask, sizeof(mask)); }

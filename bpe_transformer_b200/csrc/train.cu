@@ -105,6 +105,7 @@ struct TrainState {
     uint32_t first_new_id, vocab_size;
     uint32_t flags;  // bit 0: never use the shared-memory cache (experiments)
     uint32_t watchdog_s;
+    int driver_sm;  // -1: block 0 drives
     volatile uint32_t* beat;  // pinned host memory: [2 * cta] = iteration, [2 * cta + 1] = phase (what the host prints if the loop stalls)
     // ---- heavy steps shared between the GPUs of one box (csrc/train.cu header) ----
     uint32_t rank, world;              // world == 1: everything below is unused
@@ -690,13 +691,21 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_words = S.ctrl->n_words;
 
-    if (blockIdx.x != 0) {  // helper CTAs: asleep on the barrier until the driver broadcasts a heavy step
+    // Which CTA drives: block 0, or (experiments: BPE_B200_TRAIN_DRIVER_SM) the CTA that runs on a given SM — the loop is pure
+    // latency, and the distance from the driver's SM to the L2 slices differs between SMs of a two-die part.
+    bool is_driver = blockIdx.x == 0;
+    if (!CLUSTER && S.driver_sm >= 0 && gridDim.x > (unsigned)S.driver_sm) {
+        unsigned int smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        is_driver = (int)smid == S.driver_sm;
+    }
+    if (!is_driver) {  // helper CTAs: asleep on the barrier until the driver broadcasts a heavy step
         for (uint32_t round = 0;; round++) {
-            if (tid == 0 && blockIdx.x < 16) { S.beat[2 * blockIdx.x] = round; S.beat[2 * blockIdx.x + 1] = 20; }
+            if (tid == 0 && blockIdx.x < 16 && blockIdx.x > 0) { S.beat[2 * blockIdx.x] = round; S.beat[2 * blockIdx.x + 1] = 20; }
             if (tid == 0 && (S.flags & 16u)) { S.beat[64 + 2 * blockIdx.x] = round; S.beat[64 + 2 * blockIdx.x + 1] = 20; }
             helper_wait();
             if (tid == 0) {
-                if (blockIdx.x < 16) S.beat[2 * blockIdx.x + 1] = 21;
+                if (blockIdx.x < 16 && blockIdx.x > 0) S.beat[2 * blockIdx.x + 1] = 21;
                 const volatile Command* c = &S.ctrl->cmd;
                 sh_cmd.op = c->op; sh_cmd.a = c->a; sh_cmd.b = c->b; sh_cmd.x = c->x; sh_cmd.list_tok = c->list_tok;
                 sh_cmd.list_len = c->list_len; sh_cmd.threshold = c->threshold; sh_cmd.heavy_id = c->heavy_id;
@@ -706,7 +715,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
             if (cmd.op == 0) return;
             if (cmd.op == 2) apply_remote_hits<NT>(S, cmd);
             else heavy_rewrite<NT>(S, cmd, n_words, Q);
-            if (tid == 0 && blockIdx.x < 16) S.beat[2 * blockIdx.x + 1] = 22;
+            if (tid == 0 && blockIdx.x < 16 && blockIdx.x > 0) S.beat[2 * blockIdx.x + 1] = 22;
             if (tid == 0 && (S.flags & 16u)) S.beat[64 + 2 * blockIdx.x + 1] = 22;
             helper_done();
         }
@@ -1311,6 +1320,8 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
     for (auto& p : parts) { *p.p = base + at; at += (p.bytes + 255) / 256 * 256; }
     if (const char* f = getenv("BPE_B200_TRAIN_FLAGS")) S.flags = (uint32_t)atoi(f);
     S.watchdog_s = 120;
+    S.driver_sm = -1;
+    if (const char* f = getenv("BPE_B200_TRAIN_DRIVER_SM")) S.driver_sm = atoi(f);  // only meaningful with one CTA on every SM
     if (const char* f = getenv("BPE_B200_TRAIN_WATCHDOG")) S.watchdog_s = (uint32_t)std::max(1, atoi(f));
     const char* trace_path = getenv("BPE_B200_TRAIN_TRACE");
     uint32_t* d_trace = S.trace;

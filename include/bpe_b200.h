@@ -209,6 +209,13 @@ int bpe_decode_noalloc(const void* d_ids, int id_elem_bytes, uint64_t n_ids, con
                        const uint64_t* d_vocab_off, uint32_t n_vocab, uint8_t* d_bytes, uint64_t cap,
                        uint64_t* n_bytes, void* stream, char* h_err, size_t h_err_cap);
 
+/* Test hook (no counterpart in the reference): the 64-bit keys the library names pretokens by are ANDed with `mask` from now on
+ * (all contexts of this process on this device; all ones = normal operation).  With a narrow mask distinct pretokens share keys;
+ * the calls that add pretokens to the table (bpe_pretokenize_count, bpe_count, bpe_unique_import) and bpe_encode then return
+ * BPE_ERR_HASH_COLLISION instead of merging them: the table's identity is the BYTES (the reference's Counter is keyed by the
+ * bytes, pretokenization.py:201-207), the key only finds them.  Reset the table (bpe_unique_reset) after changing the mask. */
+int bpe_debug_key_mask(bpe_ctx* ctx, uint64_t mask);
+
 /* Kernels launched on this context since the last bpe_set_profiling(): fills up to `max` entries of
  * (name, milliseconds, launches); returns the number of entries.  Launches are always counted; milliseconds
  * (CUDA events on the launching stream) only while profiling is on. */

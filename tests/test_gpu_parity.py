@@ -237,6 +237,41 @@ def test_count_edge_sizes(engine, n):
         assert gpu_counter(engine, data, specials) == c_oracle.count(data, specials)
 
 
+def test_key_collisions_are_reported_not_merged(engine, gpt2_model):
+    """The table of distinct pretokens is found by 64-bit key but identified by BYTES.  With the keys narrowed to 10 bits (test
+    hook) thousands of distinct pretokens share keys: counting, importing and encoding must raise the collision error, never
+    hand back merged counts or another pretoken's ids.  With the full key again, everything is as before."""
+    from bpe_transformer_b200 import _lib
+    from adapters import get_tokenizer
+
+    data = synth_corpus(1, 55, 2_000_000)
+    want = c_oracle.count(data, [EOT])
+    assert len(want) > 20_000
+    engine.set_special_tokens(_lib.sort_specials([EOT]))
+    d_text, n = engine.to_device(data)
+    engine.unique_reset()
+    engine.pretokenize_count(d_text, n)
+    blob, off, ln, cnt = engine.unique_export()
+    try:
+        engine.debug_key_mask(0x3FF)
+        for count in (lambda: engine.pretokenize_count(d_text, n), lambda: engine.count(d_text, n, engine.scan(d_text, n)),
+                      lambda: engine.unique_import(blob, off, ln, cnt)):
+            engine.unique_reset()
+            with pytest.raises(_lib.BpeError) as err:
+                count()
+            assert err.value.code == _lib.ERR_HASH_COLLISION
+        engine.unique_reset()
+        vocab, merges = gpt2_model
+        tok = get_tokenizer(with_specials(vocab, [EOT]), merges, [EOT])
+        with pytest.raises(_lib.BpeError) as err:
+            tok.encode(data[:200_000].decode("utf-8", errors="ignore"))
+        assert err.value.code == _lib.ERR_HASH_COLLISION
+    finally:
+        engine.debug_key_mask(0xFFFFFFFFFFFFFFFF)
+        engine.unique_reset()
+    assert gpu_counter(engine, data, [EOT]) == want
+
+
 def test_count_accumulates_over_shards(engine):
     """bpe_count per shard (cut at special-token starts) == one call over the whole text."""
     data = synth_corpus(0, 21, 3_000_000)
