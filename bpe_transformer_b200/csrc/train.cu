@@ -543,13 +543,13 @@ __device__ __forceinline__ void send_hit(const TrainState& S, uint32_t parity, u
         if (p != S.rank) peer_entry(S, p, parity, S.rank)[at] = key;  // a store into peer memory: over NVLink, no reply awaited
 }
 
-template <int NT>
+template <int NT, bool SHARED_STEPS>
 __device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t n_words, Queue& Q) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gsize = gridDim.x * NT;
     const uint2* list = cmd.list_tok == NONE ? nullptr : S.wl_pool + __ldcg(S.wl_off + cmd.list_tok);
     const uint32_t n_cand = list ? cmd.list_len : n_words;
     const GlobalAdder add{S, cmd.threshold};
-    const bool sharded = S.world > 1;  // every GPU filters the words it owns and tells the others what it found
+    const bool sharded = SHARED_STEPS && S.world > 1;  // every GPU filters the words it owns and tells the others what it found
     const uint32_t parity = cmd.heavy_id & 1u;
     for (uint32_t base = blockIdx.x * NT; base < n_cand; base += gsize) {
         if (tid == 0) Q.n = 0;
@@ -619,7 +619,8 @@ __device__ void apply_remote_hits(const TrainState& S, const Command& cmd) {
     }
 }
 
-template <bool CLUSTER, int NT>
+// SHARED_STEPS: the variant that shares heavy steps with the other GPUs of the box (kept out of the single-GPU kernel's code).
+template <bool CLUSTER, int NT, bool SHARED_STEPS = false>
 __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
     // Driver <-> helper hand-over around a heavy step.  CLUSTER: the hardware cluster barrier on both sides.  Otherwise
     // (a cooperative grid, one CTA per SM): helpers poll a counter in global memory, so the driver's light steps involve
@@ -641,7 +642,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
         else {
             __syncthreads();
             if (threadIdx.x == 0) {
-                if (S.world > 1) __threadfence_system(); else __threadfence();  // sharded: the CTA's stores into peer memory come first, for everyone
+                if (SHARED_STEPS && S.world > 1) __threadfence_system(); else __threadfence();  // shared steps: the CTA's stores into peer memory come first, for everyone
                 atomicAdd(&S.ctrl->done, 1u);
             }
         }
@@ -713,8 +714,8 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
             __syncthreads();
             const Command cmd = sh_cmd;
             if (cmd.op == 0) return;
-            if (cmd.op == 2) apply_remote_hits<NT>(S, cmd);
-            else heavy_rewrite<NT>(S, cmd, n_words, Q);
+            if (SHARED_STEPS && cmd.op == 2) apply_remote_hits<NT>(S, cmd);
+            else heavy_rewrite<NT, SHARED_STEPS>(S, cmd, n_words, Q);
             if (tid == 0 && blockIdx.x < 16 && blockIdx.x > 0) S.beat[2 * blockIdx.x + 1] = 22;
             if (tid == 0 && (S.flags & 16u)) S.beat[64 + 2 * blockIdx.x + 1] = 22;
             helper_done();
@@ -1125,12 +1126,12 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
             if (beats && tid == 0) S.beat[1] = 8;
             if (tracer) { c3 = clock64(); h2 = c3; }
             const Command cmd{1u, a, b, x, list_tok, list_len, T, n_heavy, 0u};
-            heavy_rewrite<NT>(S, cmd, n_words, Q);
+            heavy_rewrite<NT, SHARED_STEPS>(S, cmd, n_words, Q);
             if (tracer) h3 = clock64();
             if (beats && tid == 0) S.beat[1] = 9;
             driver_join();
             if (tracer) h4 = clock64();
-            if (S.world > 1) {
+            if (SHARED_STEPS && S.world > 1) {
                 // ---- the exchange: every GPU has filtered and rewritten its share and put the keys of its hits into the peers'
                 // buffers; now the counts go out (behind the hits: system-wide fence), the peers' counts come in, and the
                 // peers' hits are rewritten here too.  Same step on every GPU: they all run the same loop on the same data.
@@ -1400,6 +1401,7 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
         if (const char* env = getenv("BPE_B200_TRAIN_NT")) nt = atoi(env);
         void (*kern)(TrainState) = nt == 1024 ? merge_loop_kernel<false, 1024> : nt == 256 ? merge_loop_kernel<false, 256> : merge_loop_kernel<false, 512>;
         if (nt != 1024 && nt != 256) nt = 512;
+        if (sharded) { kern = merge_loop_kernel<false, 512, true>; nt = 512; }
         int per_sm = 0;
         CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DriverShared)));
         CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt, sizeof(DriverShared)));
