@@ -19,8 +19,9 @@ LIB_PATH = CSRC / "libbpe_b200.so"
 
 TEXT_PAD = 64
 CUT_AFTER_NEWLINE = 1
+FAIL_ON_CR = 2  # bpe_encode: error 9 if the text holds a '\r' (a text-mode file handle would have translated it)
 
-OK, ERR_CUDA, ERR_INVALID_UTF8, ERR_CAPACITY, ERR_ARGUMENT, ERR_HASH_COLLISION, ERR_MISSING_ID, ERR_NO_PAIRS, ERR_STATE = range(9)
+OK, ERR_CUDA, ERR_INVALID_UTF8, ERR_CAPACITY, ERR_ARGUMENT, ERR_HASH_COLLISION, ERR_MISSING_ID, ERR_NO_PAIRS, ERR_STATE, ERR_CARRIAGE_RETURN = range(10)
 
 SYMBOLS = [
     "bpe_ctx_create", "bpe_ctx_destroy", "bpe_last_error", "bpe_ctx_configure", "bpe_set_special_tokens", "bpe_scan",
@@ -38,6 +39,10 @@ class BpeError(RuntimeError):
 
 
 class InvalidUtf8(BpeError):
+    pass
+
+
+class CarriageReturn(BpeError):
     pass
 
 
@@ -153,6 +158,8 @@ class Engine:
         msg = (self.lib.bpe_last_error(self.ctx) or b"").decode()
         if rc == ERR_INVALID_UTF8:
             raise InvalidUtf8(rc, msg)
+        if rc == ERR_CARRIAGE_RETURN:
+            raise CarriageReturn(rc, msg)
         raise BpeError(rc, msg)
 
     def _stream(self):

@@ -38,11 +38,33 @@ void* ctx_scratch(bpe_ctx* ctx, int which, size_t bytes) {
     return ctx->scratch[which];
 }
 
+// A few words from device memory to the host WITHOUT the copy engine: one tiny kernel stores them into page-locked,
+// device-mapped host memory.  A 4-byte cudaMemcpyAsync would queue on the device-to-host copy engine behind whatever
+// bulk copy is in flight there (bpe_store_to_host of the previous piece's ids: more than a millisecond), and every
+// call of the encode pipeline reads a status word and a total.
+__global__ void read_words_kernel(const uint32_t* __restrict__ src, int n_words, const uint32_t* __restrict__ status, volatile uint32_t* host) {
+    const int t = threadIdx.x;
+    if (t < n_words) host[1 + t] = src[t];
+    if (t == 0) host[0] = status ? *status : 0;
+    __threadfence_system();
+}
+
+// status word (0x80000000 on a CUDA error) + n_words 32-bit words of d_src (may be NULL / 0) into h_dst; synchronises s
+uint32_t ctx_read_words(bpe_ctx* ctx, cudaStream_t s, const void* d_src, int n_words, void* h_dst) {
+    if (n_words > 30) return 0x80000000u;
+    if (!ctx->h_read) {
+        if (cudaHostAlloc((void**)&ctx->h_read, 32 * sizeof(uint32_t), cudaHostAllocMapped) != cudaSuccess) return 0x80000000u;
+        if (cudaHostGetDevicePointer((void**)&ctx->d_read, (void*)ctx->h_read, 0) != cudaSuccess) return 0x80000000u;
+    }
+    read_words_kernel<<<1, 32, 0, s>>>((const uint32_t*)d_src, n_words, ctx->d_status, ctx->d_read);
+    if (cudaGetLastError() != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess) return 0x80000000u;
+    if (n_words) memcpy(h_dst, (const void*)(ctx->h_read + 1), (size_t)n_words * 4);
+    return ctx->h_read[0];
+}
+
 uint32_t ctx_read_status(bpe_ctx* ctx, cudaStream_t s, bool clear) {
-    uint32_t st = 0;
-    if (cudaMemcpyAsync(&st, ctx->d_status, 4, cudaMemcpyDeviceToHost, s) != cudaSuccess) return 0x80000000u;
-    if (cudaStreamSynchronize(s) != cudaSuccess) return 0x80000000u;
-    if (st && clear) cudaMemsetAsync(ctx->d_status, 0, 4, s);
+    uint32_t st = ctx_read_words(ctx, s, nullptr, 0, nullptr);
+    if (st && st != 0x80000000u && clear) cudaMemsetAsync(ctx->d_status, 0, 4, s);
     return st;
 }
 
@@ -58,6 +80,7 @@ int ctx_status_to_code(bpe_ctx* ctx, uint32_t st) {
     if (st & ST_WATCHDOG) return ctx_fail(ctx, BPE_ERR_CUDA, "merge loop watchdog: no progress for 60 s (internal error)");
     if (st & ST_LIST_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "posting pool full");
     if (st & ST_BLOB_FULL) return ctx_fail(ctx, BPE_ERR_CAPACITY, "token byte pool full");
+    if (st & ST_HAS_CR) return ctx_fail(ctx, BPE_ERR_CARRIAGE_RETURN, "the text holds a carriage return (BPE_FAIL_ON_CR)");
     return ctx_fail(ctx, BPE_ERR_CUDA, "unknown status bits");
 }
 
@@ -136,6 +159,7 @@ void bpe_ctx_destroy(bpe_ctx* ctx) {
     cudaFree(ctx->d_idpool);
     for (auto& p : ctx->scratch) cudaFree(p);
     if (ctx->h_beat) cudaFreeHost(ctx->h_beat);
+    if (ctx->h_read) cudaFreeHost((void*)ctx->h_read);
     peer_release(ctx);
     cudaFree(ctx->peer_buf);
     delete ctx;
@@ -382,14 +406,25 @@ int bpe_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint64_t* 
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     *n_out = 0;
     if (n == 0) return BPE_OK;
+    if (flags & BPE_FAIL_ON_CR) {
+        int rc = launch_find_byte(ctx, d_text, n, '\r', ST_HAS_CR, s);
+        if (rc) return rc;
+        if (d_start) {  // no scan of ours follows whose status read would report it
+            rc = ctx_status_to_code(ctx, ctx_read_status(ctx, s));
+            if (rc) return rc;
+        }
+    }
     if (!d_start) {
         uint32_t* mask = (uint32_t*)ctx_scratch(ctx, 6, (n / 32 + 2) * 4);
         if (!mask) return BPE_ERR_CUDA;
-        int rc = bpe_scan(ctx, d_text, n, d_cuts, n_cuts, flags, mask, stream);
+        // cold table: split and count in one pass over the text; warm table: the split alone, the emit pass does the rest
+        const bool cold = !ctx->enc_warm;
+        int rc = cold ? bpe_pretokenize_count(ctx, d_text, n, d_cuts, n_cuts, flags, mask, stream)
+                      : bpe_scan(ctx, d_text, n, d_cuts, n_cuts, flags, mask, stream);
         if (rc) return rc;
-        d_start = mask;
+        return run_encode(ctx, d_text, n, mask, d_out, out_elem_bytes, cap, n_out, s, cold);
     }
-    return run_encode(ctx, d_text, n, d_start, d_out, out_elem_bytes, cap, n_out, s);
+    return run_encode(ctx, d_text, n, d_start, d_out, out_elem_bytes, cap, n_out, s, false);
 }
 
 int bpe_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_ids, const uint8_t* h_vocab_blob,

@@ -21,6 +21,7 @@ enum : uint32_t {
     ST_LIST_FULL = 1u << 6,
     ST_WATCHDOG = 1u << 7,
     ST_ENC_MISS = 1u << 8,  // encode: a pretoken of the text is not in the table yet (handled inside bpe_encode)
+    ST_HAS_CR = 1u << 10,   // bpe_encode with BPE_FAIL_ON_CR: the text holds a '\r'
     ST_BLOB_FULL = 1u << 9,  // train: the pool of token byte strings is full (handled inside bpe_train: larger pool, run again)
 };
 
@@ -303,6 +304,8 @@ struct bpe_ctx {
     // scratch reused across calls
     void* scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    volatile uint32_t* h_read = nullptr;  // api.cu ctx_read_words: mapped host words small results are stored to
+    uint32_t* d_read = nullptr;
     uint32_t* h_beat = nullptr;  // train.cu: pinned host words the merge loop writes its progress to
     // sharded heavy steps (bpe_peer_*): this GPU's exchange buffer, the peers' buffers (opened through CUDA IPC), sizes
     void* peer_buf = nullptr;
@@ -321,6 +324,8 @@ int ctx_fail(bpe_ctx* ctx, int code, const char* what, cudaError_t e = cudaSucce
 void* ctx_scratch(bpe_ctx* ctx, int which, size_t bytes);  // grows-only device scratch, nullptr on failure
 int ctx_status_to_code(bpe_ctx* ctx, uint32_t st);
 uint32_t ctx_read_status(bpe_ctx* ctx, cudaStream_t s, bool clear = true);
+uint32_t ctx_read_words(bpe_ctx* ctx, cudaStream_t s, const void* d_src, int n_words, void* h_dst);
+int launch_find_byte(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, uint8_t byte, uint32_t status_bit, cudaStream_t s);
 
 #define CUDA_TRY(ctx, expr)                                                      \
     do {                                                                         \
@@ -373,6 +378,6 @@ int launch_export(bpe_ctx* ctx, uint8_t* d_blob, uint64_t* d_off, uint32_t* d_le
 int run_train(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_id, const uint8_t* h_init_blob, const uint32_t* h_init_off,
               uint32_t* h_merge_a, uint32_t* h_merge_b, uint32_t* n_merges, cudaStream_t s);
 int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, void* d_out, int out_elem_bytes,
-               uint64_t cap, uint64_t* n_out, cudaStream_t s);
+               uint64_t cap, uint64_t* n_out, cudaStream_t s, bool pre_counted);
 int run_decode(bpe_ctx* ctx, const void* d_ids, int id_elem_bytes, uint64_t n_ids, const uint8_t* h_vocab_blob,
                const uint64_t* h_vocab_off, uint32_t n_vocab, uint8_t* d_bytes, uint64_t cap, uint64_t* n_bytes, cudaStream_t s);

@@ -386,10 +386,11 @@ __global__ void __launch_bounds__(ENC_THREADS) decode_write_kernel(const IdT* __
 static int encode_new_pretokens(bpe_ctx* ctx, cudaStream_t s) {
     uint64_t slots = ctx->ut.cap_mask + 1;
     uint64_t h_counters[4];
-    CUDA_TRY(ctx, cudaMemcpyAsync(h_counters, ctx->ut.counters, sizeof(h_counters), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(ctx, cudaStreamSynchronize(s));
-    uint32_t st = ctx_read_status(ctx, s);
-    if (st) return ctx_status_to_code(ctx, st);
+    uint32_t st = ctx_read_words(ctx, s, ctx->ut.counters, 8, h_counters);  // no copy engine: api.cu
+    if (st) {
+        if (st != 0x80000000u) cudaMemsetAsync(ctx->d_status, 0, 4, s);
+        return ctx_status_to_code(ctx, st);
+    }
     const uint64_t n_unique = h_counters[1];
     if (n_unique <= ctx->enc_done) return BPE_OK;
     MergeTable M{ctx->d_mkey, ctx->d_mrank, ctx->d_mid, ctx->m_mask};
@@ -415,7 +416,7 @@ static int encode_new_pretokens(bpe_ctx* ctx, cudaStream_t s) {
 }
 
 int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_start, void* d_out, int out_elem_bytes,
-               uint64_t cap, uint64_t* n_out, cudaStream_t s) {
+               uint64_t cap, uint64_t* n_out, cudaStream_t s, bool pre_counted) {
     *n_out = 0;
     if (n == 0) return BPE_OK;
     EmitParams P;
@@ -432,10 +433,11 @@ int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* 
     }
     // With a warm table (every pretoken of earlier texts is cached with its ids) the text goes straight to the emit pass;
     // if it meets a pretoken it does not know, the text is counted, the new pretokens are encoded, and the emit runs again.
+    // pre_counted: the caller already counted this text into the table (one pass with the split, api.cu).
     bool counted = false;
     for (int attempt = 0; attempt < 2; attempt++) {
         if (!ctx->enc_warm || attempt == 1) {
-            int rc = launch_count(ctx, d_text, n, d_start, s);
+            int rc = pre_counted ? BPE_OK : launch_count(ctx, d_text, n, d_start, s);
             if (rc) return rc;
             rc = encode_new_pretokens(ctx, s);
             if (rc) return rc;
@@ -451,9 +453,8 @@ int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* 
             CUDA_TRY(ctx, cudaGetLastError());
         }
         unsigned long long total = 0;
-        CUDA_TRY(ctx, cudaMemcpyAsync(&total, total_out, 8, cudaMemcpyDeviceToHost, s));
-        CUDA_TRY(ctx, cudaStreamSynchronize(s));
-        uint32_t st = ctx_read_status(ctx, s);
+        uint32_t st = ctx_read_words(ctx, s, total_out, 2, &total);  // total and status in one round trip, no copy engine
+        if (st && st != 0x80000000u) cudaMemsetAsync(ctx->d_status, 0, 4, s);
         if ((st & ST_ENC_MISS) && !counted) { ctx->enc_warm = false; continue; }  // cold table: count, then emit again
         if (st & ~ST_ENC_MISS) { ctx->enc_warm = false; return ctx_status_to_code(ctx, st & ~ST_ENC_MISS); }
         if (st & ST_ENC_MISS) {  // counted, yet without an encoding: encode_new_kernel could not encode it

@@ -20,7 +20,7 @@
 #include "pretok.cuh"
 
 #ifndef FC_WARPS
-#define FC_WARPS 16
+#define FC_WARPS 20
 #endif
 #define FC_THREADS (FC_WARPS * 32)
 #define FC_SLOTS 8192            // per-CTA table: 8 B key + 4 B count

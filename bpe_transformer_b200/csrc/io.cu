@@ -26,7 +26,12 @@ namespace {
 // Every lane is one host thread with its own copy stream and two pinned buffers: while the DMA engine drains one buffer the
 // thread fills (or empties) the other.  Lanes take chunks off a shared counter and never wait for one another.
 constexpr int kMaxLanes = 16;
-constexpr size_t kLaneBytes = 2u << 20;  // small enough that the DMA engine starts early in every call, large enough for full PCIe rate
+// small enough that the DMA engine starts early in every call, large enough for full PCIe rate (BPE_B200_IO_CHUNK_KB: developer override)
+static size_t lane_bytes_from_env() {
+    if (const char* e = getenv("BPE_B200_IO_CHUNK_KB")) { long v = atol(e); if (v >= 64 && v <= (64 << 10)) return (size_t)v << 10; }
+    return 2u << 20;
+}
+static const size_t kLaneBytes = lane_bytes_from_env();
 
 struct Staging {
     int lanes = 0;

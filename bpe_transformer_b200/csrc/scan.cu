@@ -94,6 +94,34 @@ __global__ void cuts_to_mask_kernel(const uint64_t* __restrict__ cuts, uint64_t 
 
 }  // namespace
 
+// Does the text hold `byte`?  (bpe_encode's BPE_FAIL_ON_CR.)  16 bytes per thread and step, grid-stride; the buffer's
+// padding lets the last load run past n, the tail bytes are masked out.
+__global__ void __launch_bounds__(256) find_byte_kernel(const uint8_t* __restrict__ text, uint64_t n, uint32_t pattern, uint32_t bit, uint32_t* status) {
+    const uint64_t n_vec = (n + 15) / 16;
+    uint32_t hit = 0;
+    for (uint64_t v = blockIdx.x * 256ull + threadIdx.x; v < n_vec; v += (uint64_t)gridDim.x * 256) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(text) + v);
+        uint32_t w[4] = {q.x ^ pattern, q.y ^ pattern, q.z ^ pattern, q.w ^ pattern};
+        #pragma unroll
+        for (int k = 0; k < 4; k++) {
+            uint32_t z = (w[k] - 0x01010101u) & ~w[k] & 0x80808080u;  // 0x80 in (at least) every byte that was zero
+            const uint64_t at = v * 16 + k * 4;
+            if (at + 4 > n) z &= at >= n ? 0u : (0xFFFFFFFFu >> (8 * (at + 4 - n)));
+            hit |= z;
+        }
+    }
+    if (__any_sync(0xFFFFFFFFu, hit != 0) && (threadIdx.x & 31) == 0) atomicOr(status, bit);
+}
+
+int launch_find_byte(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, uint8_t byte, uint32_t status_bit, cudaStream_t s) {
+    if (!n) return BPE_OK;
+    KernelTimer t(ctx, "find_byte_kernel", s);
+    const uint64_t want = (n / 16 + 255) / 256;
+    find_byte_kernel<<<(unsigned)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)BPE_N_SM * 8)), 256, 0, s>>>(d_text, n, byte * 0x01010101u, status_bit, ctx->d_status);
+    CUDA_TRY(ctx, cudaGetLastError());
+    return BPE_OK;
+}
+
 int launch_scan(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* d_cutmask, uint32_t flags, uint32_t* d_start, cudaStream_t s) {
     CUDA_TRY(ctx, cudaMemsetAsync(d_start + (n / 32), 0, 2 * sizeof(uint32_t), s));
     if (n == 0) return BPE_OK;

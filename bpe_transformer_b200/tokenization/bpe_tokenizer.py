@@ -313,10 +313,11 @@ class BPETokenizer(Tokenizer):
                 d_text, n = load.piece(k)  # blocks until piece k has landed; later pieces keep arriving meanwhile
                 if not n:
                     continue
-                if bool((d_text[:n] == 13).any().item()):
+                try:  # the '\r' check runs on the GPU inside the call: no small device-to-host copy queues behind the ids' DMA
+                    ids = self.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE | _lib.FAIL_ON_CR, engine=engine, on_device=(d_text, n))
+                except _lib.CarriageReturn:
                     has_cr = True
                     break
-                ids = self.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=engine, on_device=(d_text, n))
                 to_store.put((ids, total))
                 total += int(ids.numel())
         except BaseException as e:  # noqa: BLE001

@@ -34,10 +34,14 @@ typedef struct bpe_ctx bpe_ctx;
                                    bpe_tokenizer.py:290) or a byte / special token has no id (:175, :206) */
 #define BPE_ERR_NO_PAIRS 7      /* nothing to merge (reference: AttributeError, bpe_trainer.py:237-240) */
 #define BPE_ERR_STATE 8         /* call order: e.g. bpe_encode() before bpe_load_model() */
+#define BPE_ERR_CARRIAGE_RETURN 9 /* bpe_encode() with BPE_FAIL_ON_CR met a '\r' in the text; nothing was encoded */
 
 /* flags for bpe_scan() / bpe_encode() */
 #define BPE_CUT_AFTER_NEWLINE 1u /* a segment boundary after every '\n': BPETokenizer.encode_iterable over
                                     an iterable of lines (bpe_tokenizer.py:368-379) */
+#define BPE_FAIL_ON_CR 2u        /* bpe_encode() only: return BPE_ERR_CARRIAGE_RETURN if the text holds a '\r'.  For callers
+                                    that stand in for a text-mode file handle, which would translate "\r\n" and "\r" to
+                                    "\n" before the reference sees the lines: they translate on the host and call again */
 
 /* Every text buffer handed to the library must be readable for BPE_TEXT_PAD bytes past its end
  * (contents irrelevant), and aligned to 16 bytes. */

@@ -497,6 +497,36 @@ def test_encode_with_a_caller_made_start_mask_equals_the_one_pass_path(engine, t
             assert np.array_equal(got, want)
 
 
+def test_encode_fail_on_cr_flag(engine, ts10k_model):
+    """BPE_FAIL_ON_CR: bpe_encode refuses a text that holds a '\\r' anywhere (first byte, last byte, last byte of a 16-byte
+    group, with or without a caller's mask) and encodes as usual when it holds none — also when a '\\r' sits just behind
+    the end, in the buffer's padding."""
+    from adapters import get_tokenizer
+    from bpe_transformer_b200 import _lib
+
+    vocab, merges = ts10k_model
+    tok = get_tokenizer(with_specials(vocab, [EOT]), merges, [EOT])
+    tok._bind(engine)
+    base = synth_corpus(0, 5, 100_003)
+    want = np.asarray(c_oracle.COracleTokenizer(tok.vocab, merges, [EOT]).encode_bytes(base, flags=1), dtype=np.uint16)
+    flags = _lib.CUT_AFTER_NEWLINE | _lib.FAIL_ON_CR
+    for cut in (len(base), 4096, 4097, 4111, 15, 1):
+        d_text, n = engine.to_device(base[:cut] + b"\r\r\r")  # the three '\r' are beyond n: padding, not text
+        got = engine.encode(d_text, cut, flags=flags).cpu().numpy().view(np.uint16)
+        if cut == len(base):
+            assert np.array_equal(got, want)
+    for at in (0, 1, 15, 16, 4095, len(base) - 1):
+        data = bytearray(base)
+        data[at] = 13
+        d_text, n = engine.to_device(bytes(data))
+        for mask in (None, engine.scan(d_text, n, flags=1)):
+            with pytest.raises(_lib.CarriageReturn):
+                engine.encode(d_text, n, flags=flags, mask=mask)
+        assert engine.encode(d_text, n, flags=1).numel() > 0  # without the flag the byte is ordinary whitespace
+    d_text, n = engine.to_device(base)
+    assert np.array_equal(engine.encode(d_text, n, flags=flags).cpu().numpy().view(np.uint16), want)  # the status word was cleared
+
+
 def test_encode_with_a_freshly_trained_vocab(tmp_path):
     """train on the GPU, encode with the result, check both against the port."""
     from adapters import get_tokenizer, run_train_bpe

@@ -14,7 +14,7 @@ eng = _lib.get_engine(0)
 eng.set_special_tokens(_lib.sort_specials([bench.EOT]))
 d_text, n = eng.load_file(path)
 eng.unique_reset()
-eng.count(d_text, n, eng.scan(d_text, n))
+eng.pretokenize_count(d_text, n)
 tr = BPETrainer(vocab_size=10000, special_tokens=[bench.EOT])
 tr._merge_tokens(eng)
 del d_text
@@ -28,15 +28,24 @@ def wrap(name):
     setattr(eng, name, g)
 for name in ("load_file", "encode", "store_into"):
     wrap(name)
-for rep in range(3):
+_ranges = eng.load_file_ranges
+class TimedLoad:
+    def __init__(self, inner): self.inner = inner
+    def piece(self, k):
+        t0 = time.perf_counter(); r = self.inner.piece(k); events.append(("wait_piece", t0, time.perf_counter())); return r
+    def join(self): return self.inner.join()
+eng.load_file_ranges = lambda *a, **k: TimedLoad(_ranges(*a, **k))
+import numpy as np
+pinned = _lib.pinned_array(int(nbytes * 0.28) + 4096, np.uint16)
+for rep in range(4):
     events.clear()
     torch.cuda.synchronize(); t0 = time.perf_counter()
-    ids = tok.encode_file_to_array(path, engine=eng)
+    ids = tok.encode_file_to_array(path, engine=eng, out=pinned)
     dt = time.perf_counter() - t0
     print(f"rep {rep}: {dt * 1e3:.1f} ms, {len(ids)} ids", flush=True)
 busy = {}
 for name, a, b in events:
     busy[name] = busy.get(name, 0) + (b - a)
 print("busy ms:", {k: round(v * 1e3, 1) for k, v in busy.items()})
-for name, a, b in sorted(events, key=lambda e: e[1])[:24]:
+for name, a, b in sorted(events, key=lambda e: e[1])[:60]:
     print(f"  {name:10s} {1e3 * (a - t0):7.2f} -> {1e3 * (b - t0):7.2f}  ({1e3 * (b - a):.2f} ms)")

@@ -16,7 +16,7 @@ eng = _lib.get_engine(0)
 eng.set_special_tokens(_lib.sort_specials([bench.EOT]))
 d_text, n = eng.load_file(path)
 eng.unique_reset()
-eng.count(d_text, n, eng.scan(d_text, n))
+eng.pretokenize_count(d_text, n)
 tr = BPETrainer(vocab_size=10000, special_tokens=[bench.EOT])
 tr._merge_tokens(eng)
 tok = BPETokenizer(tr.vocab, tr.merges, [bench.EOT])

@@ -15,7 +15,7 @@ eng.set_special_tokens(_lib.sort_specials([bench.EOT]))
 d_text, n = eng.load_file(path)
 for _ in range(reps):
     eng.unique_reset()
-    eng.count(d_text, n, eng.scan(d_text, n))
+    eng.pretokenize_count(d_text, n)
     tr = BPETrainer(vocab_size=10000, special_tokens=[bench.EOT])
     tr._merge_tokens(eng)
     print(tr.last_timing, flush=True)

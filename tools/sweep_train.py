@@ -22,8 +22,7 @@ for ctas in sys.argv[2:] or ["0"]:
     for rep in range(2):
         eng.unique_reset()
         eng.set_profiling(True)
-        mask = eng.scan(d_text, n)
-        eng.count(d_text, n, mask)
+        eng.pretokenize_count(d_text, n)
         tr = BPETrainer(vocab_size=10000, special_tokens=[bench.EOT])
         tr._merge_tokens(eng)
         kt = eng.kernel_times()
@@ -31,14 +30,13 @@ for ctas in sys.argv[2:] or ["0"]:
         ref = tr.merges
     print(f"ctas={ctas}: merge loop {tr.last_timing['merge_loop_ms']:.1f} ms, {tr.last_timing['iterations']} iterations, "
           f"{tr.last_timing['merge_loop_ms'] * 1e3 / max(1, len(tr.merges)):.2f} us/merge, same={tr.merges == ref}, "
-          f"scan {kt['scan_kernel'][0]:.2f} ms count {kt['count_kernel'][0]:.2f} ms", flush=True)
+          f"count {kt['fused_count_kernel'][0]:.2f} ms", flush=True)
 for mode in ("cluster", "grid"):
     os.environ["BPE_B200_TRAIN_MODE"] = mode
     os.environ.pop("BPE_B200_TRAIN_CTAS", None)
     for rep in range(2):
         eng.unique_reset()
-        mask = eng.scan(d_text, n)
-        eng.count(d_text, n, mask)
+        eng.pretokenize_count(d_text, n)
         tr = BPETrainer(vocab_size=10000, special_tokens=[bench.EOT])
         tr._merge_tokens(eng)
     print(f"mode={mode}: merge loop {tr.last_timing['merge_loop_ms']:.1f} ms, {tr.last_timing['iterations']} iterations, "

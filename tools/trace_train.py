@@ -18,7 +18,7 @@ for rep in range(2):
     if rep == 1:
         os.environ["BPE_B200_TRAIN_TRACE"] = out
     eng.unique_reset()
-    eng.count(d_text, n, eng.scan(d_text, n))
+    eng.pretokenize_count(d_text, n)
     tr = BPETrainer(vocab_size=10000, special_tokens=[bench.EOT])
     tr._merge_tokens(eng)
 t = np.loadtxt(out, dtype=np.int64)
