@@ -219,7 +219,7 @@ def run_reference(args, rank: int, world: int) -> None:
         enc = cpu_encode_sample(path, full["_vocab"], full["_merges"], min(total, 16_000_000), min(total, 2_000_000))
         line["encode"] = {"metric": "encode_GBps_corpus_to_uint16", "value": enc["value"], "unit": "GB/s", "variant": enc["variant"], "cores": enc["cores"],
                           "sample": enc["sample"]}
-    print(json.dumps(line), flush=True)
+    emit_line(line)
 
 
 def workload_config(total: int, world: int) -> dict:
@@ -485,7 +485,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
     dominant = min(hbm_kernels, key=hbm_kernels.get) if hbm_kernels else None
     # DRAM bytes per launch from the committed `ncu --set full` capture (tools/ncu_summary.py); only quoted for the
     # corpus size it was taken on, one GPU.
-    traffic_file = ROOT / "profiles" / "r01_ncu_dram_bytes_per_launch_2.1GB.json"
+    traffic_file = ROOT / "profiles" / "r02_ncu_dram_bytes_per_launch_2.1GB.json"
     ncu_traffic = {}
     if traffic_file.exists() and world == 1 and abs(total - 2_100_000_403) < 1_000_000:
         ncu_traffic = json.loads(traffic_file.read_text())
@@ -501,7 +501,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
                                                   "algorithmic_bytes_per_launch": emit_bytes}
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": hbm_kernels[dominant], "peak": peak, "unit": "GB/s",
                     "frac": hbm_kernels[dominant] / peak, "traffic": ncu_traffic.get(ncu_name[dominant]), "peak_source": peak_src,
-                    "traffic_source": "profiles/r01_ncu_dram_bytes_per_launch_2.1GB.json (ncu --set full, dram read + write, per launch)" if ncu_traffic else None,
+                    "traffic_source": "profiles/r02_ncu_dram_bytes_per_launch_2.1GB.json (ncu --set full, dram read + write, per launch)" if ncu_traffic else None,
                     "algorithmic_bytes_per_launch": n_local,
                     "note": "scan/count/emit are instruction-issue bound, not HBM bound (DESIGN.md section 4); the merge loop is latency bound and reported as us_per_merge",
                     "others": others}
@@ -587,10 +587,32 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
                                                                                           "ids_equal_full_corpus", "ids_equal_first_64MB"))
             + f"; cpu encode {enc_cpu['value'] * 1e3:.2f} MB/s ({enc_cpu['variant']}); CPU side took {time.perf_counter() - t0:.1f} s")
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     if failed:
         log(f"[bench] PARITY FAILED: {failed}")
         raise SystemExit(3)
+
+
+_json_fd = None
+
+
+def guard_stdout():
+    """stdout carries ONE JSON line: whatever a library prints to file descriptor 1 (NCCL's version banner does) goes to
+    stderr instead, and the line is written to the real stdout by emit_line()."""
+    global _json_fd
+    if _json_fd is None:
+        sys.stdout.flush()
+        _json_fd = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _json_fd is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_json_fd, data)
 
 
 def main():
@@ -610,6 +632,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    guard_stdout()
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
