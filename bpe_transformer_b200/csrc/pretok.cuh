@@ -38,7 +38,13 @@ __device__ __forceinline__ uint32_t sw_collapse(uint32_t m) { return (((m >> 7) 
 // ---- scalar helpers for the rare paths ------------------------------------------------------------------------
 // Strict UTF-8 decode of the character that contains byte `pos`.  Returns false if that byte is not part of
 // a valid sequence inside [0, n).  *lead = position of the first byte, *len = sequence length.
-static __device__ __noinline__ bool char_containing(const uint8_t* __restrict__ t, uint64_t pos, uint64_t n, uint64_t* lead, uint32_t* len, uint32_t* cp) {
+// The rarely taken helpers below are real calls in the one-pass kernel (its hot loop must stay inside the instruction
+// cache) and inlined in the mask kernel (scan.cu defines PRETOK_SLOW before including this file: a call under its CTA barriers
+// makes every warp wait for the slowest one's round trip).
+#ifndef PRETOK_SLOW
+#define PRETOK_SLOW __noinline__
+#endif
+static __device__ PRETOK_SLOW bool char_containing(const uint8_t* __restrict__ t, uint64_t pos, uint64_t n, uint64_t* lead, uint32_t* len, uint32_t* cp) {
     uint64_t p = pos;
     for (int k = 0; k < 3 && p > 0 && (t[p] & 0xC0) == 0x80; k++) p--;
     uint32_t b0 = t[p];
@@ -70,7 +76,7 @@ __device__ __forceinline__ uint32_t ascii_class(uint32_t b) {
 
 // Class of the character containing byte pos (CLS_O when the bytes are not valid UTF-8: the status word
 // reports that separately).
-static __device__ __noinline__ uint32_t class_containing(const PretokParams& P, uint64_t pos) {
+static __device__ PRETOK_SLOW uint32_t class_containing(const PretokParams& P, uint64_t pos) {
     uint32_t b = P.text[pos];
     if (b < 0x80) return ascii_class(b);
     uint64_t lead; uint32_t len, cp;
@@ -81,7 +87,7 @@ static __device__ __noinline__ uint32_t class_containing(const PretokParams& P, 
 // Length of the special token (priority order) that matches the text at p and ends before the next cut; 0 if none.
 // The bytes are compared first, eight at a time; only a match looks at the cuts: a newline inside the token (when every
 // newline is a cut — known from the token itself) or a caller's cut at p + 1 .. p + len - 1 splits it, so it is no match.
-static __device__ __noinline__ uint32_t special_len_at(const PretokParams& P, const Specials& sp, uint64_t p) {
+static __device__ PRETOK_SLOW uint32_t special_len_at(const PretokParams& P, const Specials& sp, uint64_t p) {
     uint8_t b0 = P.text[p];
     if (!((sp.first_byte_mask[b0 >> 5] >> (b0 & 31)) & 1u)) return 0;
     for (int s = 0; s < sp.n; s++) {
@@ -101,7 +107,7 @@ static __device__ __noinline__ uint32_t special_len_at(const PretokParams& P, co
 // regex.split scans left to right and continues after each match, so a candidate is a real match iff the
 // scan arrives exactly at it.  A candidate with no other candidate in the max_len-1 bytes before it cannot
 // be covered: walk back to such a chain head, then replay the scan from there.
-static __device__ __noinline__ bool special_is_real(const PretokParams& P, const Specials& sp, uint64_t p) {
+static __device__ PRETOK_SLOW bool special_is_real(const PretokParams& P, const Specials& sp, uint64_t p) {
     uint64_t head = p, j = p;
     while (j > 0) {
         j--;

@@ -10,6 +10,7 @@
 //   * non-ASCII bytes                        -> decode, two-stage class table, strict UTF-8 validation
 //   * apostrophes                            -> contraction rule 's 'd 'm 't 'll 've 're (scalar)
 // HBM traffic: N bytes read, N/8 bytes written.  Grid = persistent, a multiple of 148 SMs.
+#define PRETOK_SLOW __forceinline__
 #include "pretok.cuh"
 
 #define SCAN_THREADS 256
