@@ -229,11 +229,19 @@ __global__ void __launch_bounds__(EMIT_THREADS, 6) emit_fused_kernel(const EmitP
     EmitWarp& W = reinterpret_cast<EmitWarp*>(smem_raw)[threadIdx.x >> 5];
     const uint32_t lane = threadIdx.x & 31;
     const EmitLookup lookup{P, sp, special_first_bytes(sp)};
+    const uint32_t warp = threadIdx.x >> 5;
+    __shared__ unsigned long long sh_tile, sh_before;
+    __shared__ unsigned long long sh_ids[EMIT_WARPS];
+    const uint64_t n_tiles = (n_windows + EMIT_WARPS - 1) / EMIT_WARPS;
+    // A CTA takes a TILE of EMIT_WARPS consecutive windows per ticket, one window per warp; the chained scan below runs once
+    // per tile, in warp 0, while the other warps wait at a barrier (which costs no issue slots: with a look-back per
+    // window, a third of the kernel's instructions were polls of other windows' state words).
     for (;;) {
-        unsigned long long win = 0;
-        if (lane == 0) win = atomicAdd(ticket, 1ull);
-        win = __shfl_sync(0xFFFFFFFFu, win, 0);
-        if (win >= n_windows) return;
+        if (threadIdx.x == 0) sh_tile = atomicAdd(ticket, 1ull);
+        __syncthreads();  // also: everyone is done with the previous tile's sh_ids / sh_before
+        const unsigned long long tile = sh_tile;
+        if (tile >= n_tiles) return;
+        const unsigned long long win = tile * EMIT_WARPS + warp;  // may lie behind the last window: an empty one
         const uint64_t w0 = win * 32, wi = w0 + lane, kib = w0 * 32;
         const uint32_t w = wi < P.n_words ? __ldg(P.start + wi) : 0u;
         const uint32_t mine = __popc(w);
@@ -267,32 +275,44 @@ __global__ void __launch_bounds__(EMIT_THREADS, 6) emit_fused_kernel(const EmitP
         __syncwarp();
         unsigned long long win_ids = my_ids;
         for (int o = 16; o; o >>= 1) win_ids += __shfl_xor_sync(0xFFFFFFFFu, win_ids, o);
-        // ---- chained scan over the windows ---------------------------------------------------------------------------------
-        unsigned long long before = 0;
-        if (win == 0) {
-            if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state) = ST_INC | win_ids;
-        } else {
-            if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state + win) = ST_AGG | win_ids;
-            long long j0 = (long long)win - 1;  // lane L looks at window j0 - L
-            for (;;) {
-                const long long j = j0 - (long long)lane;
-                unsigned long long v = j >= 0 ? *reinterpret_cast<volatile unsigned long long*>(state + j) : ST_INC;  // in front of window 0: prefix 0
-                const uint32_t inc = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 2), none = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 0);
-                const uint32_t first_inc = inc ? (uint32_t)__ffs(inc) - 1 : 32;  // nearest window whose inclusive prefix is known
-                const uint32_t need = first_inc >= 31 ? 0xFFFFFFFFu : ((2u << first_inc) - 1u);
-                if (none & need) {  // a window we depend on has not published yet: look again, a little later (every
-                    __nanosleep(128);  // look is 32 loads through L2, and the warps that still have to publish need it)
-                    continue;
+        // ---- chained scan over the tiles -----------------------------------------------------------------------------------
+        if (lane == 0) sh_ids[warp] = win_ids;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned long long tile_ids = lane < EMIT_WARPS ? sh_ids[lane] : 0ull;
+            for (int o = 16; o; o >>= 1) tile_ids += __shfl_xor_sync(0xFFFFFFFFu, tile_ids, o);
+            unsigned long long before = 0;
+            if (tile == 0) {
+                if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state) = ST_INC | tile_ids;
+            } else {
+                if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state + tile) = ST_AGG | tile_ids;
+                long long j0 = (long long)tile - 1;  // lane L looks at tile j0 - L
+                for (;;) {
+                    const long long j = j0 - (long long)lane;
+                    unsigned long long v = j >= 0 ? *reinterpret_cast<volatile unsigned long long*>(state + j) : ST_INC;  // in front of tile 0: prefix 0
+                    const uint32_t inc = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 2), none = __ballot_sync(0xFFFFFFFFu, (v >> 62) == 0);
+                    const uint32_t first_inc = inc ? (uint32_t)__ffs(inc) - 1 : 32;  // nearest tile whose inclusive prefix is known
+                    const uint32_t need = first_inc >= 31 ? 0xFFFFFFFFu : ((2u << first_inc) - 1u);
+                    if (none & need) {  // a tile we depend on has not published yet: look again, a little later
+                        __nanosleep(64);
+                        continue;
+                    }
+                    unsigned long long part = (lane <= first_inc) ? (v & ~(3ull << 62)) : 0ull;
+                    for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
+                    before += part;
+                    if (first_inc < 32) break;
+                    j0 -= 32;
                 }
-                unsigned long long part = (lane <= first_inc) ? (v & ~(3ull << 62)) : 0ull;
-                for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
-                before += part;
-                if (first_inc < 32) break;
-                j0 -= 32;
+                if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state + tile) = ST_INC | (before + tile_ids);
             }
-            if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state + win) = ST_INC | (before + win_ids);
+            if (lane == 0) {
+                sh_before = before;
+                if (tile == n_tiles - 1) *total_out = before + tile_ids;
+            }
         }
-        if (win == n_windows - 1 && lane == 0) *total_out = before + win_ids;
+        __syncthreads();
+        unsigned long long before = sh_before;
+        for (uint32_t k = 0; k < warp; k++) before += sh_ids[k];
         // ---- write the ids -----------------------------------------------------------------------------------------------------
         unsigned long long running = before;
         for (uint32_t t0 = 0; t0 < total; t0 += 32) {
@@ -423,7 +443,8 @@ int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* 
     P.text = d_text; P.n = n; P.start = d_start; P.n_words = (n + 31) / 32; P.ut = ctx->ut; P.idpool = ctx->d_idpool;
     P.special_id = ctx->d_special_id; P.status = ctx->d_status;
     const uint64_t n_windows = (P.n_words + 31) / 32;
-    unsigned long long* buf = (unsigned long long*)ctx_scratch(ctx, 3, (n_windows + 4) * 8);
+    const uint64_t n_tiles = (n_windows + EMIT_WARPS - 1) / EMIT_WARPS;  // one state word of the chained scan per tile of windows
+    unsigned long long* buf = (unsigned long long*)ctx_scratch(ctx, 3, (n_tiles + 4) * 8);
     if (!buf) return BPE_ERR_CUDA;
     unsigned long long* ticket = buf, *total_out = buf + 1, *state = buf + 2;
     if (!ctx->emit_attr_set) {  // per context = per device
@@ -443,10 +464,10 @@ int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* 
             if (rc) return rc;
             counted = true;
         }
-        CUDA_TRY(ctx, cudaMemsetAsync(buf, 0, (n_windows + 4) * 8, s));
+        CUDA_TRY(ctx, cudaMemsetAsync(buf, 0, (n_tiles + 4) * 8, s));
         {
             KernelTimer t(ctx, "emit_fused_kernel", s);
-            const uint64_t blocks = std::min<uint64_t>((n_windows + EMIT_WARPS - 1) / EMIT_WARPS, (uint64_t)BPE_N_SM * 6);
+            const uint64_t blocks = std::min<uint64_t>(n_tiles, (uint64_t)BPE_N_SM * 6);
             const size_t smem = EMIT_WARPS * sizeof(EmitWarp);
             if (out_elem_bytes == 2) emit_fused_kernel<uint16_t><<<(unsigned)blocks, EMIT_THREADS, smem, s>>>(P, ctx->sp, n_windows, state, ticket, (uint16_t*)d_out, cap, total_out);
             else emit_fused_kernel<uint32_t><<<(unsigned)blocks, EMIT_THREADS, smem, s>>>(P, ctx->sp, n_windows, state, ticket, (uint32_t*)d_out, cap, total_out);
