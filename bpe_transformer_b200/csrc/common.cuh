@@ -96,6 +96,27 @@ __device__ __forceinline__ uint64_t hash_key(const uint8_t* __restrict__ base, u
     return key_finish(h);
 }
 
+// hash_key for the common case in straight-line code that all lanes of a warp run together (the loop above leaves most lanes
+// idle while the longest token of the round finishes): up to 16 bytes through three aligned 8-byte loads, funnel shifts to
+// the token's first byte and a mask behind its last one; longer tokens take the loop.  Same value as hash_key().
+__device__ __forceinline__ uint64_t hash_key_short(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
+    if (len > 16) return hash_key(base, p, len);
+    const uint2* q = reinterpret_cast<const uint2*>(base + (p & ~7ull));  // reads at most 24 bytes from there: inside BPE_TEXT_PAD
+    const uint2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+    const bool up = (p & 4u) != 0;  // the token starts in the upper half of the first 8 bytes
+    const uint32_t d0 = up ? a.y : a.x, d1 = up ? b.x : a.y, d2 = up ? b.y : b.x, d3 = up ? c.x : b.y, d4 = up ? c.y : c.x;
+    const uint32_t sh = ((uint32_t)p & 3u) * 8u;
+    uint32_t w0 = __funnelshift_r(d0, d1, sh), w1 = __funnelshift_r(d1, d2, sh), w2 = __funnelshift_r(d2, d3, sh), w3 = __funnelshift_r(d3, d4, sh);
+    const int L = (int)len;  // byte j (0..15) survives iff j < len: a clamped funnel shift of 0xFFFFFFFF by 32 - 8 * (bytes of the token in the word)
+    w0 &= __funnelshift_rc(0xFFFFFFFFu, 0u, 32u - 8u * (uint32_t)min(L, 4));
+    w1 &= __funnelshift_rc(0xFFFFFFFFu, 0u, 32u - 8u * (uint32_t)min(max(L - 4, 0), 4));
+    w2 &= __funnelshift_rc(0xFFFFFFFFu, 0u, 32u - 8u * (uint32_t)min(max(L - 8, 0), 4));
+    w3 &= __funnelshift_rc(0xFFFFFFFFu, 0u, 32u - 8u * (uint32_t)min(max(L - 12, 0), 4));
+    uint64_t h = mix64(key_seed(len), w0 | ((uint64_t)w1 << 32));
+    if (len > 8) h = mix64(h, w2 | ((uint64_t)w3 << 32));
+    return key_finish(h);
+}
+
 __device__ __forceinline__ TokenKey hash_bytes(const uint8_t* __restrict__ base, uint64_t p, uint64_t len) {
     TokenKey k;
     k.key = hash_key(base, p, len);

@@ -173,7 +173,10 @@ __global__ void __launch_bounds__(1024) scan_totals_kernel(const uint32_t* __res
 // its lanes, looks each one up (key -> table slot -> cached ids), publishes the window's id count, obtains the count of
 // all earlier windows by looking back at their published states (decoupled look-back), and writes its ids.
 // HBM traffic: N bytes of text + N/8 of mask read, 2T (or 4T) bytes of ids written; the tables sit in L2.
+#ifndef EMIT_THREADS
 #define EMIT_THREADS 256
+#endif
+#define EMIT_CTAS_PER_SM (1536 / EMIT_THREADS)
 #define EMIT_WARPS (EMIT_THREADS / 32)
 #define EMIT_KEEP 288        // tokens of a window whose table entries are kept in shared memory between the two passes
 #define ST_AGG (1ull << 62)  // state word: window's own count is available
@@ -199,7 +202,7 @@ struct EmitLookup {
             }
         }
         if (len < 0xFFFFFFFFull) {
-            const uint64_t key = hash_key(P.text, p, (uint32_t)len);
+            const uint64_t key = hash_key_short(P.text, p, (uint32_t)len);
             uint64_t slot = (key * 0xD6E8FEB86659FD93ull >> 17) & P.ut.cap_mask;  // the slot sequence of unique_find
             for (uint64_t probe = 0; probe <= P.ut.cap_mask; probe++) {
                 const uint4 e = __ldg(P.ut.enc + slot);
@@ -222,7 +225,7 @@ struct EmitLookup {
 __device__ __forceinline__ uint32_t ent_ids(uint2 e) { return (e.y >> 31) ? ((e.y >> 16) & 0x3FFFu) : e.y; }
 
 template <typename OutT>
-__global__ void __launch_bounds__(EMIT_THREADS, 6) emit_fused_kernel(const EmitParams P, const __grid_constant__ Specials sp, uint64_t n_windows,
+__global__ void __launch_bounds__(EMIT_THREADS, EMIT_CTAS_PER_SM) emit_fused_kernel(const EmitParams P, const __grid_constant__ Specials sp, uint64_t n_windows,
                                                                      unsigned long long* __restrict__ state, unsigned long long* __restrict__ ticket,
                                                                      OutT* __restrict__ out, uint64_t cap, unsigned long long* __restrict__ total_out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -467,7 +470,7 @@ int run_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint32_t* 
         CUDA_TRY(ctx, cudaMemsetAsync(buf, 0, (n_tiles + 4) * 8, s));
         {
             KernelTimer t(ctx, "emit_fused_kernel", s);
-            const uint64_t blocks = std::min<uint64_t>(n_tiles, (uint64_t)BPE_N_SM * 6);
+            const uint64_t blocks = std::min<uint64_t>(n_tiles, (uint64_t)BPE_N_SM * EMIT_CTAS_PER_SM);
             const size_t smem = EMIT_WARPS * sizeof(EmitWarp);
             if (out_elem_bytes == 2) emit_fused_kernel<uint16_t><<<(unsigned)blocks, EMIT_THREADS, smem, s>>>(P, ctx->sp, n_windows, state, ticket, (uint16_t*)d_out, cap, total_out);
             else emit_fused_kernel<uint32_t><<<(unsigned)blocks, EMIT_THREADS, smem, s>>>(P, ctx->sp, n_windows, state, ticket, (uint32_t*)d_out, cap, total_out);
