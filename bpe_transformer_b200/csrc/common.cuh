@@ -327,6 +327,8 @@ struct bpe_ctx {
     size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     volatile uint32_t* h_read = nullptr;  // api.cu ctx_read_words: mapped host words small results are stored to
     uint32_t* d_read = nullptr;
+    void* train_kern = nullptr;  // train.cu: the merge loop variant whose launch attributes are set, and its CTAs per SM
+    int train_per_sm = 0;
     uint32_t* h_beat = nullptr;  // train.cu: pinned host words the merge loop writes its progress to
     // sharded heavy steps (bpe_peer_*): this GPU's exchange buffer, the peers' buffers (opened through CUDA IPC), sizes
     void* peer_buf = nullptr;

@@ -88,6 +88,7 @@ struct Ctrl {
     unsigned long long phase_clk[8];  // developer trace: SM cycles of the driver's thread 0 per phase, summed over iterations
     unsigned long long sub_clk[8];    // developer trace: inside the argmax (scan, barrier, ties, barrier, order + barrier)
     unsigned long long heavy_clk[6];  // developer trace, heavy steps: drain, wake, own share, join, reload, rest
+    unsigned long long t_begin, t_end; // globaltimer when the driver CTA entered / left the kernel
 };
 
 struct TrainState {
@@ -1238,6 +1239,9 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
         S.ctrl->dbg[7] = smid;
         S.ctrl->cmd.op = 0;
+        unsigned long long t_now;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_now));
+        S.ctrl->t_begin = t_start; S.ctrl->t_end = t_now;
         __threadfence();
         S.beat[1] = 12;
     }
@@ -1402,12 +1406,17 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
         void (*kern)(TrainState) = nt == 1024 ? merge_loop_kernel<false, 1024> : nt == 256 ? merge_loop_kernel<false, 256> : merge_loop_kernel<false, 512>;
         if (nt != 1024 && nt != 256) nt = 512;
         if (sharded) { kern = merge_loop_kernel<false, 512, true>; nt = 512; }
-        int per_sm = 0;
-        CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DriverShared)));
-        CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt, sizeof(DriverShared)));
-        cudaDeviceProp prop;
-        CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, ctx->device));
-        int grid = per_sm >= 1 ? prop.multiProcessorCount : 1;  // helpers poll a flag: every CTA must be resident (cooperative launch)
+        // Between the pair histogram and this launch the GPU is idle: nothing slow may sit here.  cudaGetDeviceProperties did
+        // (2.5 ms on a good call, up to 100 ms on a bad one: the run-to-run outliers of round 1); the SM count is the
+        // context's, the attribute and the occupancy answer are kept per kernel variant.
+        if (ctx->train_kern != (void*)kern) {
+            int per_sm = 0;
+            CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DriverShared)));
+            CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, nt, sizeof(DriverShared)));
+            ctx->train_kern = (void*)kern;
+            ctx->train_per_sm = per_sm;
+        }
+        int grid = ctx->train_per_sm >= 1 ? ctx->n_sm : 1;  // helpers poll a flag: every CTA must be resident (cooperative launch)
         if (const char* env = getenv("BPE_B200_TRAIN_CTAS")) {
             int v = atoi(env);
             if (v >= 1 && v <= grid) grid = v;
@@ -1417,13 +1426,19 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
         CUDA_TRY(ctx, cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(nt), args, sizeof(DriverShared), s));
         launched_ctas = grid;
     }
+    double host_wait = 0, host_max_gap = 0;
+    unsigned host_polls = 0;
     {   // wait with a deadline
         cudaEvent_t done;
         cudaEventCreateWithFlags(&done, cudaEventDisableTiming);
         cudaEventRecord(done, s);
         auto t0 = std::chrono::steady_clock::now();
+        double last_poll = 0;
         while (cudaEventQuery(done) == cudaErrorNotReady) {
             double waited = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            host_max_gap = std::max(host_max_gap, waited - last_poll);
+            last_poll = waited;
+            host_polls++;
             if (waited > S.watchdog_s + 10.0) {
                 fprintf(stderr, "[bpe_train rank %s] merge loop stalled: driver at iteration %u phase %u;", getenv("RANK") ? getenv("RANK") : "-", h_beat[0], h_beat[1]);
                 for (int c = 1; c < launched_ctas && c < 16; c++) fprintf(stderr, " cta%d round %u phase %u;", c, h_beat[2 * c], h_beat[2 * c + 1]);
@@ -1439,6 +1454,7 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
             }
             if (waited > 0.002) std::this_thread::sleep_for(std::chrono::microseconds(200));
         }
+        host_wait = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         cudaEventDestroy(done);
     }
     CUDA_TRY(ctx, cudaMemcpyAsync(&h_ctrl, S.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, s));
@@ -1479,8 +1495,9 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
     cudaEventElapsedTime(&ms1, ev[1], ev[2]);
     ctx->train_ms[0] = ms0; ctx->train_ms[1] = ms1; ctx->train_ms[2] = h_ctrl.n_iters;
     if (getenv("BPE_B200_TRAIN_VERBOSE"))
-        fprintf(stderr, "[bpe_train] merge loop %.2f ms, %u iterations, %u heavy steps, %u rebuilds, driver CTA on SM %u\n", ms1, h_ctrl.n_iters,
-                h_ctrl.n_heavy, h_ctrl.n_rebuilds, h_ctrl.dbg[7]);
+        fprintf(stderr, "[bpe_train] merge loop %.2f ms, %u iterations, %u heavy steps, %u rebuilds, driver CTA on SM %u; driver CTA inside the kernel %.2f ms; "
+                        "host waited %.2f ms in %u polls, longest gap between polls %.2f ms\n", ms1, h_ctrl.n_iters,
+                h_ctrl.n_heavy, h_ctrl.n_rebuilds, h_ctrl.dbg[7], (h_ctrl.t_end - h_ctrl.t_begin) / 1e6, host_wait * 1e3, host_polls, host_max_gap * 1e3);
     for (auto& e : ev) cudaEventDestroy(e);
     const uint32_t st = ctx_read_status(ctx, s);
     if (st == ST_BLOB_FULL) { *blob_full = true; return BPE_OK; }  // nothing else went wrong: the caller retries with a larger pool

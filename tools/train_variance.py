@@ -25,6 +25,7 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 24
 out = subprocess.run([sys.executable, __file__, "child", str(reps)], capture_output=True, text=True).stderr  # the library prints to stderr
 rows = [(float(m.group(1)), int(m.group(2))) for m in re.finditer(r"merge loop ([\d.]+) ms.*driver CTA on SM (\d+)", out)]
+print(out)
 by_sm = {}
 for ms, sm in rows:
     print(f"merge loop {ms:.2f} ms, driver CTA on SM {sm}")
