@@ -9,6 +9,6 @@ python bench.py > gpurun_out/${t}_bench.json 2> gpurun_out/${t}_bench.log; echo 
 python bench.py --steps 2 --warmup 3 --no-cpu > /dev/null 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${t}_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/${t}_launches.log 2>&1; echo "launch list rc=$?"
-python tools/run_encode_once.py 2100000000 1 0 > gpurun_out/${t}_once.log 2>&1 && \
+python tools/run_encode_once.py 2100000000 2 0 > gpurun_out/${t}_once.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:'fused_count|scan_kernel|emit_fused' -o gpurun_out/${t}_full \
-    python tools/run_encode_once.py 2100000000 1 0 > gpurun_out/${t}_full.log 2>&1; echo "ncu full rc=$?"; tail -2 gpurun_out/${t}_full.log
+    python tools/run_encode_once.py 2100000000 2 0 > gpurun_out/${t}_full.log 2>&1; echo "ncu full rc=$?"; tail -2 gpurun_out/${t}_full.log

@@ -10,6 +10,10 @@ src_csv, cubin, kname = sys.argv[1], sys.argv[2], sys.argv[3]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 rows = list(csv.reader(open(src_csv)))
 hdr, data = rows[1], rows[2:]
+for i, r in enumerate(data):  # a report with several matching launches: one block per launch, each opened by a 'Kernel Name' row
+    if r and r[0] == "Kernel Name":
+        data = data[:i]
+        break
 iE, iT, iW = hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed"), hdr.index("Warp Stall Sampling (All Samples)")
 dis = subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout.splitlines()
 # find the section of the kernel
