@@ -19,7 +19,8 @@ _MISSING = 0xFFFFFFFF
 _BATCH_BYTES = 64 << 20  # encode_iterable hands the GPU about this much text at a time
 
 
-_PIPE_BYTES = int(os.environ.get("BPE_B200_PIPE_BYTES", str(128 << 20)))  # piece size of the load / encode / store pipeline
+_PIPE_BYTES = int(os.environ.get("BPE_B200_PIPE_BYTES", str(128 << 20)))  # largest piece of the load / encode / store pipeline
+_PIPE_MIN_BYTES = 16 << 20  # smallest: a rank's share of a file is cut into about eight pieces, so that the three stages overlap
 _FIRST_BATCH_BYTES = 1 << 20  # encode_iterable over arbitrary chunks: first ids after ~1 MB of text, batches double up to _BATCH_BYTES
 _serials = itertools.count(1)  # one number per tokenizer object, never reused (id() is: CPython recycles addresses)
 
@@ -262,20 +263,21 @@ class BPETokenizer(Tokenizer):
             want = np.uint32 if self._model()[6] else np.uint16
             if out.ndim != 1 or out.dtype != want or not out.flags.c_contiguous or not out.flags.writeable:
                 raise ValueError(f"out must be a writable 1-D C-contiguous {np.dtype(want).name} array")
-        if cut_after_newline and hi - lo > _PIPE_BYTES + _PIPE_BYTES // 2:
-            ids = self._encode_file_pipelined(path, lo, hi, engine, out)
+        piece = min(_PIPE_BYTES, max(_PIPE_MIN_BYTES, (hi - lo) // 8))
+        if cut_after_newline and hi - lo > piece + piece // 2:
+            ids = self._encode_file_pipelined(path, lo, hi, engine, out, piece)
             if ids is not None:
                 return ids
         return self.encode_device_to_array(engine.load_file(path, lo, hi), engine, cut_after_newline, out)
 
-    def _encode_file_pipelined(self, path, lo: int, hi: int, engine: "_lib.Engine", out: np.ndarray | None = None):
+    def _encode_file_pipelined(self, path, lo: int, hi: int, engine: "_lib.Engine", out: np.ndarray | None = None, piece: int = 0):
         """None if the file holds a '\\r' (the caller then takes the whole-file path with newline translation)."""
         import queue
         import threading
 
         import torch
 
-        offs = _cuts_after_newlines(path, lo, hi, _PIPE_BYTES)
+        offs = _cuts_after_newlines(path, lo, hi, piece or _PIPE_BYTES)
         wide = self._bind(engine)
         if out is None:
             out = _lib.host_array(hi - lo, np.uint32 if wide else np.uint16)  # one id per byte at most; unused pages stay untouched
