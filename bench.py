@@ -461,7 +461,10 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
     eng.set_profiling(True)
     train_step_resident()
     k_train = eng.kernel_times()
-    eng.set_profiling(True)
+    eng.set_profiling(True)  # the training above emptied the pretoken table: this encode is a first one (split + count in one pass, new pretokens encoded) ...
+    tok.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=eng, on_device=(d_enc, n_enc))
+    k_enc_first = eng.kernel_times()
+    eng.set_profiling(True)  # ... and this one runs with the cache warm, like the timed calls
     tok.encode_bytes_to_device(None, flags=_lib.CUT_AFTER_NEWLINE, engine=eng, on_device=(d_enc, n_enc))
     k_enc = eng.kernel_times()
     eng.set_profiling(False)
@@ -481,6 +484,8 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
         kernels[name] = {"ms": ms, "launches": n}
     for name, (ms, n) in k_enc.items():
         kernels["encode:" + name] = {"ms": ms, "launches": n}
+    for name, (ms, n) in k_enc_first.items():
+        kernels["encode_first_call:" + name] = {"ms": ms, "launches": n}
     hbm_kernels = {k: gbps(n_local, k_train[k][0]) for k in ("fused_count_kernel", "scan_kernel", "count_kernel") if k in k_train and k_train[k][0]}
     dominant = min(hbm_kernels, key=hbm_kernels.get) if hbm_kernels else None
     # DRAM bytes per launch from the committed `ncu --set full` capture (tools/ncu_summary.py); only quoted for the
@@ -499,6 +504,11 @@ def run_gpu(args, rank: int, world: int, local_rank: int) -> None:
             v = gbps(emit_bytes, k_enc["emit_fused_kernel"][0])
             others["encode:emit_fused_kernel"] = {"achieved": v, "frac": v / peak, "traffic": ncu_traffic.get(ncu_name["emit_fused_kernel"]),
                                                   "algorithmic_bytes_per_launch": emit_bytes}
+        if k_enc.get("scan_kernel", (0, 0))[0]:
+            scan_bytes = int(n_enc + n_enc // 8)  # N read + N/8 of mask written
+            v = gbps(scan_bytes, k_enc["scan_kernel"][0])
+            others["encode:scan_kernel"] = {"achieved": v, "frac": v / peak, "traffic": ncu_traffic.get("scan_kernel<1>"),
+                                            "algorithmic_bytes_per_launch": scan_bytes}
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": hbm_kernels[dominant], "peak": peak, "unit": "GB/s",
                     "frac": hbm_kernels[dominant] / peak, "traffic": ncu_traffic.get(ncu_name[dominant]), "peak_source": peak_src,
                     "traffic_source": "profiles/r02_ncu_dram_bytes_per_launch_2.1GB.json (ncu --set full, dram read + write, per launch)" if ncu_traffic else None,
