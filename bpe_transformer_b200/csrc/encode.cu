@@ -177,6 +177,9 @@ __global__ void __launch_bounds__(1024) scan_totals_kernel(const uint32_t* __res
 #define EMIT_THREADS 256
 #endif
 #define EMIT_CTAS_PER_SM (1536 / EMIT_THREADS)
+#ifndef EMIT_SLEEP_NS
+#define EMIT_SLEEP_NS 64  // pause between two looks at the state words of earlier tiles
+#endif
 #define EMIT_WARPS (EMIT_THREADS / 32)
 #define EMIT_KEEP 288        // tokens of a window whose table entries are kept in shared memory between the two passes
 #define ST_AGG (1ull << 62)  // state word: window's own count is available
@@ -297,7 +300,7 @@ __global__ void __launch_bounds__(EMIT_THREADS, EMIT_CTAS_PER_SM) emit_fused_ker
                     const uint32_t first_inc = inc ? (uint32_t)__ffs(inc) - 1 : 32;  // nearest tile whose inclusive prefix is known
                     const uint32_t need = first_inc >= 31 ? 0xFFFFFFFFu : ((2u << first_inc) - 1u);
                     if (none & need) {  // a tile we depend on has not published yet: look again, a little later
-                        __nanosleep(64);
+                        __nanosleep(EMIT_SLEEP_NS);
                         continue;
                     }
                     unsigned long long part = (lane <= first_inc) ? (v & ~(3ull << 62)) : 0ull;

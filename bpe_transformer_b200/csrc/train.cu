@@ -44,8 +44,15 @@ namespace cg = cooperative_groups;
 
 #define PAIR_PROBE_LIMIT 8192
 #define RETIRED (-(1ll << 62))  // count of a pair that was merged (or found to have no occurrence): never positive again
-#define LIGHT_MAX 2048u         // posting lists up to this length are handled by the driver CTA alone
+#ifndef LIGHT_MAX
+#define LIGHT_MAX 2048u         // posting lists up to this length are handled by the driver CTA alone (measured: 1024 / 1536 / 2048 / 3072 / 4096 -> 90.9 / 88.9 / 87.6 / 91.4 / 93.3 ms)
+#endif
+#ifndef QUEUE_CAP
 #define QUEUE_CAP 2048u
+#endif
+#ifndef HELPER_SLEEP_NS
+#define HELPER_SLEEP_NS 32   // helper CTAs look at the driver's flag this often while the driver works alone (measured: 16 / 32 / 64 / 256 / 1024 ns -> 86.9 / 86.8 / 87.3 / 87.6 / 88.4 ms)
+#endif
 #define NONE 0xFFFFFFFFu
 #define MAX_TIES 1024u            // pairs that tie at the top count and are ordered by their bytes
 #define W_MASK 0x1FFFFFFFu        // a posting's word index; the three bits above it name the GPU that filters the word in a sharded heavy step
@@ -631,7 +638,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
         if constexpr (CLUSTER) cg::this_cluster().sync();
         else {
             if (threadIdx.x == 0) {
-                while (*reinterpret_cast<volatile unsigned int*>(&S.ctrl->go) == seen) __nanosleep(256);
+                while (*reinterpret_cast<volatile unsigned int*>(&S.ctrl->go) == seen) __nanosleep(HELPER_SLEEP_NS);
                 __threadfence();
             }
             seen++;
@@ -1282,6 +1289,9 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
     if (n_unique == 0 || n_sym + 4 * n_unique >= 0xFFFFFFF0ull || n_unique > W_MASK) return ctx_fail(ctx, n_unique ? BPE_ERR_CAPACITY : BPE_ERR_NO_PAIRS, "word table size");
     if (vocab_size < first_new_id) vocab_size = first_new_id;  // nothing to learn, but "no pairs" is still an error
 
+    // Progress words in pinned host memory (see below); allocated here, in front of everything timed: the first cudaHostAlloc of a
+    // process can take milliseconds, and the GPU would idle between the pair histogram and the loop's launch.
+    if (!ctx->h_beat) CUDA_TRY(ctx, cudaHostAlloc((void**)&ctx->h_beat, 2 * 4096 * sizeof(uint32_t), cudaHostAllocMapped));
     cudaEvent_t ev[3];
     for (auto& e : ev) cudaEventCreate(&e);
     cudaEventRecord(ev[0], s);
@@ -1372,7 +1382,6 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
     }
 
     // Progress words in pinned host memory: if the loop ever stalls the host says where instead of hanging silently.
-    if (!ctx->h_beat) CUDA_TRY(ctx, cudaHostAlloc((void**)&ctx->h_beat, 2 * 4096 * sizeof(uint32_t), cudaHostAllocMapped));
     uint32_t* h_beat = ctx->h_beat;  // per context: two engines training from two threads must not share it
     memset(h_beat, 0, 2 * 4096 * sizeof(uint32_t));
     uint32_t* d_beat = nullptr;
