@@ -113,6 +113,7 @@ struct TrainState {
     uint32_t first_new_id, vocab_size;
     uint32_t flags;  // bit 0: never use the shared-memory cache (experiments)
     uint32_t watchdog_s;
+    uint32_t cache_fill;  // entries a rebuild of the hot-pair cache aims for (the rest of its HC entries is room for pairs that rise past T)
     int driver_sm;  // -1: block 0 drives
     volatile uint32_t* beat;  // pinned host memory: [2 * cta] = iteration, [2 * cta + 1] = phase (what the host prints if the loop stalls)
     // ---- heavy steps shared between the GPUs of one box (csrc/train.cu header) ----
@@ -194,7 +195,6 @@ struct GlobalAdder {
 // light step run without touching global memory.  Entries appended during a step get their count from global memory
 // when the step closes; after a heavy step (other CTAs updated counts) all copies are reloaded.
 #define HC 4096u      // cache entries
-#define CACHE_FILL 2048u  // entries a rebuild aims for (the rest is room for pairs that rise past T)
 #define PRE_UNKNOWN (~0ull)  // HotCache::pre of an entry whose prefix key has not been fetched (yet): ties go to global memory
 #define SUB_BINS 1024u
 #define HIDX 8192u    // index slots (power of two)
@@ -787,11 +787,11 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
                 if (cnt > 0) atomicAdd(&sh_hist[63 - __clzll(cnt)], 1u);
             }
             __syncthreads();
-            if (tid == 0) {  // the bin (power of two) in which the CACHE_FILL-th largest count lies
+            if (tid == 0) {  // the bin (power of two) in which the cache_fill-th largest count lies
                 unsigned int above = sh_hist[63];
                 int bit = 63;
                 for (; bit > 0; bit--) {
-                    if (above + sh_hist[bit - 1] > CACHE_FILL) break;
+                    if (above + sh_hist[bit - 1] > S.cache_fill) break;
                     above += sh_hist[bit - 1];
                 }
                 sh_bit = bit;      // bins >= bit fit entirely (`above` pairs); bin bit - 1 does not (unless bit == 0)
@@ -811,7 +811,7 @@ __global__ void __launch_bounds__(NT, 1) merge_loop_kernel(TrainState S) {
                 if (tid == 0) {
                     unsigned int above = sh_above;
                     long long slice = (lo + width - 1) / width;  // slices in use
-                    while (slice > 0 && above + sh_sub[slice - 1] <= CACHE_FILL) above += sh_sub[--slice];
+                    while (slice > 0 && above + sh_sub[slice - 1] <= S.cache_fill) above += sh_sub[--slice];
                     sh_T = lo + slice * width;
                 }
                 __syncthreads();
@@ -1335,6 +1335,7 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
     for (auto& p : parts) { *p.p = base + at; at += (p.bytes + 255) / 256 * 256; }
     if (const char* f = getenv("BPE_B200_TRAIN_FLAGS")) S.flags = (uint32_t)atoi(f);
     S.watchdog_s = 120;
+    S.cache_fill = 0;  // chosen below, once the number of distinct pairs is known
     S.driver_sm = -1;
     if (const char* f = getenv("BPE_B200_TRAIN_DRIVER_SM")) S.driver_sm = atoi(f);  // only meaningful with one CTA on every SM
     if (const char* f = getenv("BPE_B200_TRAIN_WATCHDOG")) S.watchdog_s = (uint32_t)std::max(1, atoi(f));
@@ -1372,6 +1373,14 @@ static int run_train_once(bpe_ctx* ctx, uint32_t vocab_size, uint32_t first_new_
     CUDA_TRY(ctx, cudaMemcpyAsync(&h_ctrl, S.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(ctx, cudaStreamSynchronize(s));
     cudaEventRecord(ev[1], s);
+    // Size of the hot-pair cache.  Fewer cached pairs make every step cheaper (argmax scan, reload behind a heavy step) and
+    // rebuilds more frequent, and a rebuild walks all live pairs.  Measured (tools/cache_fill_sweep.py), 512 / 1024 / 2048 / 3072
+    // entries: 2.1 GB TinyStories-shaped, vocab 10k (2*10^5 words): 85.4 / 83.3 / 86.4 / 91.8 ms with 20 / 12 / 8 / 8 rebuilds;
+    // 11 GB OpenWebText-shaped, vocab 32k (1.9*10^7 words): 4.11 / 3.14 / 2.63 / 2.55 s with 65 / 35 / 19 / 16 rebuilds.
+    // (The table of pairs grows with the words, not with the byte pairs it starts from: the words decide.)
+    S.cache_fill = n_words < (1u << 20) ? 1024u : n_words < (1u << 23) ? 2048u : 3072u;
+    if (const char* f = getenv("BPE_B200_TRAIN_CACHE_FILL")) S.cache_fill = (uint32_t)std::min(3584, std::max(64, atoi(f)));
+    if (getenv("BPE_B200_TRAIN_VERBOSE")) fprintf(stderr, "[bpe_train] %u words, %u distinct pairs at the start, hot-pair cache aims for %u entries\n", n_words, h_ctrl.n_live, S.cache_fill);
     if (h_ctrl.n_live == 0) {
         for (auto& e : ev) cudaEventDestroy(e);
         return ctx_fail(ctx, BPE_ERR_NO_PAIRS, "no byte pairs to merge");
