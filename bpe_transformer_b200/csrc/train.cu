@@ -553,17 +553,20 @@ __device__ __forceinline__ void send_hit(const TrainState& S, uint32_t parity, u
 
 template <int NT, bool SHARED_STEPS>
 __device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t n_words, Queue& Q) {
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gsize = gridDim.x * NT;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint2* list = cmd.list_tok == NONE ? nullptr : S.wl_pool + __ldcg(S.wl_off + cmd.list_tok);
     const uint32_t n_cand = list ? cmd.list_len : n_words;
     const GlobalAdder add{S, cmd.threshold};
     const bool sharded = SHARED_STEPS && S.world > 1;  // every GPU filters the words it owns and tells the others what it found
     const uint32_t parity = cmd.heavy_id & 1u;
-    for (uint32_t base = blockIdx.x * NT; base < n_cand; base += gsize) {
+    // Candidates are dealt out evenly: a list of 5,000 postings gives every CTA of the grid a warp or two of them (and at most one
+    // round of rewriting), instead of ten CTAs 512 each (and three rounds) while the others only report back.
+    const uint32_t per = min((uint32_t)NT, max(32u, ((n_cand + gridDim.x - 1) / gridDim.x + 31u) & ~31u));
+    for (uint32_t base = blockIdx.x * per; base < n_cand; base += gridDim.x * per) {
         if (tid == 0) Q.n = 0;
         __syncthreads();
         const uint32_t i = base + tid;
-        if (i < n_cand) {
+        if (tid < per && i < n_cand) {
             uint32_t w, off, len;
             if (list) { const uint2 e = __ldcg(list + i); w = e.x; off = e.y; }
             else { w = sharded ? (i | ((uint32_t)S.w_owner[i] << W_OWNER_SHIFT)) : i; off = S.w_off[i]; }
