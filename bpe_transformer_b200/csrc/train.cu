@@ -560,17 +560,40 @@ __device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t 
     const bool sharded = SHARED_STEPS && S.world > 1;  // every GPU filters the words it owns and tells the others what it found
     const uint32_t parity = cmd.heavy_id & 1u;
     // Candidates are dealt out evenly: a list of 5,000 postings gives every CTA of the grid a warp or two of them (and at most one
-    // round of rewriting), instead of ten CTAs 512 each (and three rounds) while the others only report back.
-    const uint32_t per = min((uint32_t)NT, max(32u, ((n_cand + gridDim.x - 1) / gridDim.x + 31u) & ~31u));
-    for (uint32_t base = blockIdx.x * per; base < n_cand; base += gridDim.x * per) {
+    // round of rewriting), instead of ten CTAs 512 each (and three rounds) while the others only report back.  A thread takes
+    // up to HEAVY_R candidates per pass with their loads in flight together (postings, then symbols + lengths): an all-words step
+    // over 2*10^7 words is 126 passes instead of 252.
+    constexpr uint32_t HEAVY_R = 2;  // measured 2 / 3 / 4: 81.4 / 81.8 / 84.8 ms at 2.1 GB, 2.12 / - / 2.02 s at 11 GB; beyond 2 the kernel spills
+    const uint32_t R = n_cand > gridDim.x * NT ? HEAVY_R : 1u;  // only when one candidate per thread of the grid would take several passes
+    const uint32_t per = min((uint32_t)NT, max(32u, ((n_cand + gridDim.x * R - 1) / (gridDim.x * R) + 31u) & ~31u));  // threads in use
+    const uint32_t chunk = per * R;  // <= QUEUE_CAP
+    for (uint32_t base = blockIdx.x * chunk; base < n_cand; base += gridDim.x * chunk) {
         if (tid == 0) Q.n = 0;
         __syncthreads();
-        const uint32_t i = base + tid;
-        if (tid < per && i < n_cand) {
-            uint32_t w, off, len;
-            if (list) { const uint2 e = __ldcg(list + i); w = e.x; off = e.y; }
-            else { w = sharded ? (i | ((uint32_t)S.w_owner[i] << W_OWNER_SHIFT)) : i; off = S.w_off[i]; }
-            if ((!sharded || (w >> W_OWNER_SHIFT) == S.rank) && word_has_pair(S, w, off, cmd.a, cmd.b, &len)) {
+        uint32_t cw[HEAVY_R], coff[HEAVY_R], clen[HEAVY_R];
+        uint4 cv[HEAVY_R];
+        bool ok[HEAVY_R];
+#pragma unroll
+        for (uint32_t r = 0; r < HEAVY_R; r++) {
+            const uint32_t i = base + r * per + tid;
+            ok[r] = r < R && tid < per && i < n_cand;
+            if (ok[r]) {
+                if (list) { const uint2 e = __ldcg(list + i); cw[r] = e.x; coff[r] = e.y; }
+                else { cw[r] = sharded ? (i | ((uint32_t)S.w_owner[i] << W_OWNER_SHIFT)) : i; coff[r] = S.w_off[i]; }
+            }
+        }
+#pragma unroll
+        for (uint32_t r = 0; r < HEAVY_R; r++) {
+            ok[r] = ok[r] && (!sharded || (cw[r] >> W_OWNER_SHIFT) == S.rank);
+            if (ok[r]) {
+                cv[r] = __ldcg(reinterpret_cast<const uint4*>(S.sym + coff[r]));  // every word owns at least 4 symbol slots
+                clen[r] = __ldcg(S.w_len + (cw[r] & W_MASK));
+            }
+        }
+#pragma unroll
+        for (uint32_t r = 0; r < HEAVY_R; r++) {
+            if (ok[r] && word_has_pair_loaded(S, coff[r], cv[r], clen[r], cmd.a, cmd.b)) {
+                const uint32_t w = cw[r], off = coff[r], len = clen[r];
                 unsigned int q = atomicAdd(&Q.n, 1u);
                 if (q < QUEUE_CAP) { Q.w[q] = w; Q.off[q] = off; Q.len[q] = (unsigned short)min(len, 0xFFFFu); }
                 else if (rewrite_word_serial(S, w, off, len, cmd.a, cmd.b, cmd.x, add)) {
