@@ -50,6 +50,9 @@ namespace cg = cooperative_groups;
 #ifndef QUEUE_CAP
 #define QUEUE_CAP 2048u
 #endif
+#ifndef HEAVY_MIN_THREADS
+#define HEAVY_MIN_THREADS 32  // heavy step: a CTA that gets candidates gets at least this many
+#endif
 #ifndef HELPER_SLEEP_NS
 #define HELPER_SLEEP_NS 32   // helper CTAs look at the driver's flag this often while the driver works alone (measured: 16 / 32 / 64 / 256 / 1024 ns -> 86.9 / 86.8 / 87.3 / 87.6 / 88.4 ms)
 #endif
@@ -446,13 +449,6 @@ __device__ __forceinline__ bool word_has_pair_loaded(const TrainState& S, uint32
     return hit;
 }
 
-__device__ __forceinline__ bool word_has_pair(const TrainState& S, uint32_t w, uint32_t off, uint32_t a, uint32_t b, uint32_t* len_out) {
-    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(S.sym + off));  // every word owns at least 4 symbol slots: load before the length is known
-    const uint32_t len = __ldcg(S.w_len + (w & W_MASK));
-    *len_out = len;
-    return word_has_pair_loaded(S, off, v, len, a, b);
-}
-
 // One word, one thread: replace (a, b) by x left to right without overlap, apply the reference's count deltas.
 // Returns whether anything matched.  (Words longer than a warp, and queue overflow.)
 template <class Adder>
@@ -565,7 +561,7 @@ __device__ void heavy_rewrite(const TrainState& S, const Command& cmd, uint32_t 
     // over 2*10^7 words is 126 passes instead of 252.
     constexpr uint32_t HEAVY_R = 2;  // measured 2 / 3 / 4: 81.4 / 81.8 / 84.8 ms at 2.1 GB, 2.12 / - / 2.02 s at 11 GB; beyond 2 the kernel spills
     const uint32_t R = n_cand > gridDim.x * NT ? HEAVY_R : 1u;  // only when one candidate per thread of the grid would take several passes
-    const uint32_t per = min((uint32_t)NT, max(32u, ((n_cand + gridDim.x * R - 1) / (gridDim.x * R) + 31u) & ~31u));  // threads in use
+    const uint32_t per = min((uint32_t)NT, max((uint32_t)HEAVY_MIN_THREADS, ((n_cand + gridDim.x * R - 1) / (gridDim.x * R) + 31u) & ~31u));  // threads in use
     const uint32_t chunk = per * R;  // <= QUEUE_CAP
     for (uint32_t base = blockIdx.x * chunk; base < n_cand; base += gridDim.x * chunk) {
         if (tid == 0) Q.n = 0;
