@@ -179,7 +179,8 @@ int bpe_load_model(bpe_ctx* ctx, const uint32_t* h_a, const uint32_t* h_b, const
  * or uint32 (4); `cap` = capacity in elements; *n_out = ids produced (if > cap nothing was written and
  * BPE_ERR_CAPACITY is returned).  d_start may be NULL (the library scans into its own scratch) or a mask
  * made by bpe_scan() with the same cuts and flags.  Encodings of distinct pretokens stay cached in the
- * context across calls (the reference's _encoding_cache, bpe_tokenizer.py:57-60, 232-236). */
+ * context across calls (the reference's _encoding_cache, bpe_tokenizer.py:57-60, 232-236).  With BPE_FAIL_ON_CR in
+ * `flags` a text that holds a '\r' is refused (BPE_ERR_CARRIAGE_RETURN, nothing written). */
 int bpe_encode(bpe_ctx* ctx, const uint8_t* d_text, uint64_t n, const uint64_t* d_cuts, uint64_t n_cuts,
                uint32_t flags, const uint32_t* d_start, void* d_out, int out_elem_bytes, uint64_t cap,
                uint64_t* n_out, void* stream);
